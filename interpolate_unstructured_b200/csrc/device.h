@@ -1,0 +1,106 @@
+// device.h -- launch interface between api.cu (C ABI, pipelines) and kernels.cu (sm_100a kernels)
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "internal.h"
+
+namespace iu {
+
+// Per-cell record, device order (= kd-tree leaf-slot order), in doubles:
+//   ppc = 4 (quad, tetra), 256 B: [0..11] face normals n1..n4, [12..23] vertices p1..p4,
+//       [24,25] 4 x int32 neighbours (1-based device ids, <= 0 passed through),
+//       [26,27] 4 x int32 vertex ids (0-based), [28] volume, [29] int32 original id (1-based) + pad
+//   ppc = 3 (triangle), 192 B: [0..8] normals, [9] area, [10..18] vertices, [19] pad,
+//       [20,21] int32 {nb1, nb2, nb3, original id}, [22,23] int32 {c1, c2, c3, pad}
+template <int PPC> struct RecLayout;
+template <> struct RecLayout<4> {
+  static constexpr int STRIDE = 32, NRM = 0, PTS = 12, NBR_I = 48, CEL_I = 52, VOL = 28, ORG_I = 58;
+};
+template <> struct RecLayout<3> {
+  static constexpr int STRIDE = 24, NRM = 0, PTS = 10, NBR_I = 40, CEL_I = 44, VOL = 9, ORG_I = 43;
+};
+inline int rec_stride(int ppc) { return ppc == 3 ? RecLayout<3>::STRIDE : RecLayout<4>::STRIDE; }
+
+enum QueryMode : int {
+  QM_NEAREST = 0,       // find_nearby_cell_kdtree            -> out_i32 = nearest cell
+  QM_CELL = 1,          // iu_get_cell                         -> i_cell
+  QM_INTERP = 2,        // iu_interpolate_at                   -> i_cell, out_f64 (n_vars per query)
+  QM_CELL_F64 = 3,      // iu_get_cell_scalar_at               -> i_cell, out_f64
+  QM_CELL_I32 = 4,      // iu_get_icell_scalar_at              -> i_cell, out_i32
+  QM_INTERP_ICELL = 5   // iu_interpolate_at_icell (cells given, no search)
+};
+
+// counters (device, unsigned long long each)
+enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_N = 4 };
+
+struct DeviceGrid {
+  int cell_type = 0, ppc = 0, n_cells = 0, n_points = 0;
+  // kd-tree
+  int n_leaves = 0, n_internal = 0, n_sm_nodes = 0;
+  double* split = nullptr;
+  uint8_t* sdim = nullptr;
+  double* centers4 = nullptr;      // n_leaves*LEAF x {x, y, z, bits(original id)}; padding = +inf
+  // mesh
+  double* rec = nullptr;           // n_leaves*LEAF records
+  int32_t* dev_of_orig = nullptr;  // [n_cells + 1], index = 1-based original id -> 1-based device id
+  int32_t* orig_of_dev = nullptr;  // [n_leaves*LEAF], 1-based original id, 0 = padding
+  // data tables
+  int n_pd = 0, pd_stride = 0;
+  double* pd = nullptr;            // point-major [n_points][pd_stride]
+  int n_cd = 0, cd_cap = 0;
+  double* cd = nullptr;            // column-major (n_cells, n_cd), original cell order
+  int n_icd = 0, icd_cap = 0;
+  int32_t* icd = nullptr;          // column-major (n_cells, n_icd), original cell order
+  unsigned long long* counters = nullptr;
+  double rmin[3] = {0, 0, 0}, rmax[3] = {0, 0, 0};
+};
+
+struct QueryArgs {
+  int mode = QM_CELL;
+  int64_t n = 0;
+  const double* r = nullptr;        // (3, n)
+  const uint32_t* perm = nullptr;   // processing order (Morton-sorted), or null
+  int32_t* i_cell = nullptr;        // inout (const for QM_INTERP_ICELL)
+  double* out_f64 = nullptr;
+  int32_t* out_i32 = nullptr;
+  int n_vars = 0;
+  int ivars[MAX_VARS] = {0};        // 0-based columns
+  int max_steps = 1 << 20;
+};
+
+struct WalkArgs {
+  int64_t n = 0;
+  int max_steps = 0;
+  const double* r0 = nullptr;
+  const double* r1 = nullptr;
+  const int32_t* ic0 = nullptr;
+  int32_t* ic1 = nullptr;
+  double* r_p = nullptr;
+  int32_t* n_steps = nullptr;
+  int32_t* status = nullptr;
+  int mask_col = -1;                // 0-based icell_data column, -1 = absent
+};
+
+// every launcher returns the number of kernels it launched (for IU_B200_STAT_KERNEL_LAUNCHES)
+int launch_cell_centers(const DeviceGrid& g, const double* points, const int32_t* cells, double* centers, cudaStream_t s);
+int launch_build_records(const DeviceGrid& g, const double* points, const int32_t* cells, const int32_t* neighbors,
+                         const double* centers, cudaStream_t s);
+int launch_export_geometry(const DeviceGrid& g, double* cell_points, double* normals, double* volume, double* centers,
+                           cudaStream_t s);
+int launch_pack_point_data(const DeviceGrid& g, const double* cols, int col0, int n_cols, cudaStream_t s);
+int launch_repack_point_data(const double* old_pd, int old_stride, double* new_pd, int new_stride, int n_cols,
+                             int n_points, cudaStream_t s);
+size_t sort_temp_bytes(int64_t n, int end_bit);
+int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t* keys, uint32_t* keys_alt,
+                       uint32_t* idx, uint32_t* idx_alt, void* temp, size_t temp_bytes, int* end_bit_out,
+                       cudaStream_t s);
+int morton_end_bit(const DeviceGrid& g);
+int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s);
+int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s);
+int launch_generate_queries(int64_t n, int64_t first, uint64_t seed, const double lo[3], const double hi[3], double* r,
+                            cudaStream_t s);
+int launch_merge_rows(int64_t n, int row_bytes, const int32_t* i_cell, const void* src, void* dst, cudaStream_t s);
+
+}  // namespace iu

@@ -1,0 +1,770 @@
+// kernels.cu -- sm_100a kernels of libiu_b200.so.
+//
+// Compiled with --fmad=false: every fp64 expression below evaluates in source order with one
+// rounding per operation, exactly like the reference's `gfortran -O2` x86-64 (SSE2, no FMA)
+// build (Makefile:7-8).  fp64 '/' and sqrt() are IEEE round-to-nearest on the device.  Branch
+// decisions (face choice, walk termination, nearest centre) are therefore bit-identical to the
+// reference arithmetic restated in oracle/iu_oracle.cpp.
+//
+// Kernels:
+//   k_cell_centers     iu_get_cell_center for every cell (input of the kd-tree build)
+//   k_build_records    set_cell_points + set_face_normal_vectors + set_cell_volumes -> 256/192-B
+//                      per-cell records in kd-tree leaf order, plus the leaf centre blocks
+//   k_morton_keys      Morton key of each query for the coherence sort (cub radix sort follows)
+//   k_query<...>       THE hot kernel: [kd-tree nearest centre | hint] -> ray walk -> interpolate
+//   k_walk<...>        iu_get_cell_through_neighbors with explicit r0 / ic0 / mask outputs
+//   k_pack_point_data, k_export_geometry, k_generate_queries: plumbing
+#include <cub/device/device_radix_sort.cuh>
+
+#include "device.h"
+
+namespace iu {
+
+namespace {
+
+constexpr double TINY_DISTANCE = 1e-100;   // m_interp_unstructured.f90:20
+constexpr double HUGE_DISTANCE = 1e100;    // :738
+constexpr int QUERY_THREADS = 256;
+constexpr int MAX_SM_NODES = 2047;         // top 11 tree levels staged in shared memory
+
+struct V3 { double x, y, z; };
+__device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ V3 neg(V3 a) { return {-a.x, -a.y, -a.z}; }
+// Fortran dot_product: ((a1*b1 + a2*b2) + a3*b3)
+__device__ __forceinline__ double dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+// cross_product, :644-651
+__device__ __forceinline__ V3 cross(V3 a, V3 b) {
+  return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ double cross_z(V3 a, V3 b) { return a.x * b.y - a.y * b.x; }   // :654-657
+__device__ __forceinline__ double stp(V3 a, V3 b, V3 c) { return dot3(a, cross(b, c)); }    // :659-662
+
+// gfortran NORM2: running-scale algorithm with scale starting at 1.  While all
+// |x_i| <= 1 the scale never changes and val = |x_i| / 1 is exact, so the result is
+// sqrt(x1^2 + x2^2 + x3^2) summed in order: that is the fast path.
+__device__ __forceinline__ double norm2_3(V3 v) {
+  const double ax = fabs(v.x), ay = fabs(v.y), az = fabs(v.z);
+  if (ax <= 1.0 && ay <= 1.0 && az <= 1.0) return sqrt((ax * ax + ay * ay) + az * az);
+  double scale = 1.0, s = 0.0;
+  const double a[3] = {ax, ay, az};
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    if (a[i] != 0.0) {
+      if (scale < a[i]) {
+        const double val = scale / a[i];
+        s = 1.0 + s * val * val;
+        scale = a[i];
+      } else {
+        const double val = a[i] / scale;
+        s += val * val;
+      }
+    }
+  }
+  return scale * sqrt(s);
+}
+
+__device__ __forceinline__ V3 ld3(const double* p) { return {__ldg(p), __ldg(p + 1), __ldg(p + 2)}; }
+
+// ------------------------------------------------------------------------------------------------
+// set-up kernels
+// ------------------------------------------------------------------------------------------------
+template <int PPC>
+__device__ __forceinline__ V3 center_of(const V3* p) {
+  V3 s = p[0];
+#pragma unroll
+  for (int k = 1; k < PPC; ++k) s = s + p[k];
+  const double d = (double)PPC;
+  return {s.x / d, s.y / d, s.z / d};   // sum(cell_points, dim=2) / n_points_per_cell, :268
+}
+
+template <int PPC>
+__global__ void k_cell_centers(int n_cells, const double* __restrict__ points, const int32_t* __restrict__ cells,
+                               double* __restrict__ centers) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cells) return;
+  V3 p[PPC];
+#pragma unroll
+  for (int k = 0; k < PPC; ++k) p[k] = ld3(points + 3 * (size_t)(cells[(size_t)c * PPC + k] - 1));
+  const V3 ce = center_of<PPC>(p);
+  centers[3 * (size_t)c] = ce.x; centers[3 * (size_t)c + 1] = ce.y; centers[3 * (size_t)c + 2] = ce.z;
+}
+
+__global__ void k_fill_dev_of_orig(int n_slots, const int32_t* __restrict__ orig_of_dev, int32_t* __restrict__ dev_of_orig) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_slots) return;
+  const int o = orig_of_dev[s];
+  if (o > 0) dev_of_orig[o] = s + 1;
+}
+
+// One thread per device slot: gathers the cell's vertices and derives normals / volume with the
+// reference's arithmetic (set_cell_points :291-302, set_face_normal_vectors :306-370,
+// set_cell_volumes :372-410).
+template <int PPC, int CT>
+__global__ void k_build_records(int n_slots, const int32_t* __restrict__ orig_of_dev, const int32_t* __restrict__ dev_of_orig,
+                                const double* __restrict__ points, const int32_t* __restrict__ cells,
+                                const int32_t* __restrict__ neighbors, const double* __restrict__ centers,
+                                double* __restrict__ rec, double* __restrict__ centers4) {
+  using L = RecLayout<PPC>;
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_slots) return;
+  const int o = orig_of_dev[s];
+  double* R = rec + (size_t)s * L::STRIDE;
+  double* C4 = centers4 + 4 * (size_t)s;
+  if (o <= 0) {   // padding slot of the last leaf block: never the nearest, never visited
+    const double inf = __longlong_as_double(0x7ff0000000000000LL);
+    C4[0] = inf; C4[1] = inf; C4[2] = inf; C4[3] = 0.0;
+    for (int i = 0; i < L::STRIDE; ++i) R[i] = 0.0;
+    return;
+  }
+  const size_t c = (size_t)(o - 1);
+  V3 p[PPC];
+  int32_t pid[PPC];
+#pragma unroll
+  for (int k = 0; k < PPC; ++k) {
+    pid[k] = cells[c * PPC + k] - 1;
+    p[k] = ld3(points + 3 * (size_t)pid[k]);
+  }
+  const V3 center = center_of<PPC>(p);
+  V3 normal_cell{0, 0, 0};
+  if (CT != IU_TETRA_CT) normal_cell = cross(p[1] - p[0], p[2] - p[1]);          // :322-324
+#pragma unroll
+  for (int k = 0; k < PPC; ++k) {
+    const int k1 = (k + 1) % PPC, k2 = (k + 2) % PPC;
+    V3 nf;
+    if (CT != IU_TETRA_CT) nf = cross(p[k1] - p[k], normal_cell);               // :329-330
+    else nf = cross(p[k1] - p[k], p[k2] - p[k1]);                               // :351-353
+    if (dot3(p[k] - center, nf) < 0) nf = neg(nf);                              // :333-334, :356-357
+    const double len = norm2_3(nf);
+    R[L::NRM + 3 * k] = nf.x / len; R[L::NRM + 3 * k + 1] = nf.y / len; R[L::NRM + 3 * k + 2] = nf.z / len;
+    R[L::PTS + 3 * k] = p[k].x; R[L::PTS + 3 * k + 1] = p[k].y; R[L::PTS + 3 * k + 2] = p[k].z;
+  }
+  double vol;
+  if (CT == IU_TRIANGLE_CT) vol = 0.5 * norm2_3(cross(p[1] - p[0], p[2] - p[0]));
+  else if (CT == IU_QUAD_CT) {
+    const double a1 = 0.5 * norm2_3(cross(p[1] - p[0], p[2] - p[0]));
+    const double a2 = 0.5 * norm2_3(cross(p[2] - p[0], p[PPC - 1] - p[0]));
+    vol = a1 + a2;
+  } else {
+    const double sixth = 1 / 6.0;
+    vol = sixth * stp(p[1] - p[0], p[2] - p[0], p[PPC - 1] - p[0]);
+  }
+  R[L::VOL] = vol;
+  int32_t* RI = reinterpret_cast<int32_t*>(R);
+#pragma unroll
+  for (int k = 0; k < PPC; ++k) {
+    const int nb = neighbors[c * PPC + k];
+    RI[L::NBR_I + k] = nb >= 1 ? dev_of_orig[nb] : nb;
+    RI[L::CEL_I + k] = pid[k];
+  }
+  RI[L::ORG_I] = o;
+  if (PPC == 4) { RI[L::ORG_I + 1] = 0; R[30] = 0.0; R[31] = 0.0; }
+  else { R[19] = 0.0; RI[L::CEL_I + 3] = 0; }
+  // leaf centre block entry; the centre is the array the tree was built from (bit-identical to
+  // sum(cell_points)/ppc at :429)
+  C4[0] = centers[3 * c]; C4[1] = centers[3 * c + 1]; C4[2] = centers[3 * c + 2];
+  C4[3] = __longlong_as_double((long long)o);
+}
+
+template <int PPC>
+__global__ void k_export_geometry(int n_slots, const int32_t* __restrict__ orig_of_dev, const double* __restrict__ rec,
+                                  const double* __restrict__ centers4, double* cell_points, double* normals,
+                                  double* volume, double* centers) {
+  using L = RecLayout<PPC>;
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_slots) return;
+  const int o = orig_of_dev[s];
+  if (o <= 0) return;
+  const double* R = rec + (size_t)s * L::STRIDE;
+  const size_t c = (size_t)(o - 1);
+  for (int i = 0; i < 3 * PPC; ++i) {
+    if (cell_points) cell_points[c * 3 * PPC + i] = R[L::PTS + i];
+    if (normals) normals[c * 3 * PPC + i] = R[L::NRM + i];
+  }
+  if (volume) volume[c] = R[L::VOL];
+  if (centers) for (int i = 0; i < 3; ++i) centers[3 * c + i] = centers4[4 * (size_t)s + i];
+}
+
+// column-major host layout (n_points, n_cols) -> point-major device table
+__global__ void k_pack_point_data(int n_points, int n_cols, int col0, int stride, const double* __restrict__ cols,
+                                  double* __restrict__ pd) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_points * n_cols) return;
+  const int v = (int)(i / n_points);
+  const size_t p = i % n_points;
+  pd[p * stride + col0 + v] = cols[i];
+}
+
+__global__ void k_repack_point_data(int n_points, int n_cols, int old_stride, int new_stride, const double* __restrict__ a,
+                                    double* __restrict__ b) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_points * new_stride) return;
+  const size_t p = i / new_stride;
+  const int v = (int)(i % new_stride);
+  b[i] = v < n_cols ? a[p * old_stride + v] : 0.0;
+}
+
+__device__ __forceinline__ uint64_t splitmix64(uint64_t idx, uint64_t seed) {
+  uint64_t z = (idx + seed) * 0x9E3779B97F4A7C15ULL;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  return z ^ (z >> 31);
+}
+
+__global__ void k_generate_queries(int64_t n, int64_t first, uint64_t seed, double lox, double loy, double loz, double hix,
+                                   double hiy, double hiz, double* __restrict__ r) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 3 * n) return;
+  const int k = (int)(i % 3);
+  const double u = (double)(splitmix64((uint64_t)(i + 3 * first), seed) >> 11) * (1.0 / 9007199254740992.0);
+  const double lo = k == 0 ? lox : k == 1 ? loy : loz;
+  const double hi = k == 0 ? hix : k == 1 ? hiy : hiz;
+  r[i] = lo + u * (hi - lo);
+}
+
+// dst row i <- src row i where i_cell[i] >= 1 (rows of not-found queries stay untouched)
+__global__ void k_merge_rows(int64_t n, int row_words, const int32_t* __restrict__ i_cell, const uint32_t* __restrict__ src,
+                             uint32_t* __restrict__ dst) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * row_words) return;
+  if (i_cell[i / row_words] >= 1) dst[i] = src[i];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Morton keys
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t spread3(uint32_t v) {   // 10 bits -> every third bit
+  v &= 0x3ffu;
+  v = (v | (v << 16)) & 0x030000ffu;
+  v = (v | (v << 8)) & 0x0300f00fu;
+  v = (v | (v << 4)) & 0x030c30c3u;
+  v = (v | (v << 2)) & 0x09249249u;
+  return v;
+}
+__device__ __forceinline__ uint32_t spread2(uint32_t v) {   // 16 bits -> every second bit
+  v &= 0xffffu;
+  v = (v | (v << 8)) & 0x00ff00ffu;
+  v = (v | (v << 4)) & 0x0f0f0f0fu;
+  v = (v | (v << 2)) & 0x33333333u;
+  v = (v | (v << 1)) & 0x55555555u;
+  return v;
+}
+__device__ __forceinline__ uint32_t quantise(double x, double lo, double scale, uint32_t maxv) {
+  const double t = (x - lo) * scale;
+  if (!(t > 0.0)) return 0u;   // also NaN
+  return t >= (double)maxv ? maxv : (uint32_t)t;
+}
+
+// bits = bits per dimension; planar meshes (z extent 0) use a 2-D key
+__global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lox, double loy, double loz, double sx,
+                              double sy, double sz, int bits, int planar, uint32_t* __restrict__ keys,
+                              uint32_t* __restrict__ idx) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t maxv = (1u << bits) - 1u;
+  const uint32_t ix = quantise(__ldg(r + 3 * i), lox, sx, maxv);
+  const uint32_t iy = quantise(__ldg(r + 3 * i + 1), loy, sy, maxv);
+  uint32_t key;
+  if (planar) key = spread2(ix) | (spread2(iy) << 1);
+  else {
+    const uint32_t iz = quantise(__ldg(r + 3 * i + 2), loz, sz, maxv);
+    key = spread3(ix) | (spread3(iy) << 1) | (spread3(iz) << 2);
+  }
+  keys[i] = key;
+  idx[i] = (uint32_t)i;
+}
+
+// ------------------------------------------------------------------------------------------------
+// device-side pieces of the hot path
+// ------------------------------------------------------------------------------------------------
+struct TreeView {
+  const double* split;
+  const uint8_t* sdim;
+  const double* centers4;
+  int n_internal;
+  int n_sm_nodes;
+};
+
+// Exact nearest centre (squared distance summed x, y, z without FMA, like kdtree2's leaf loop);
+// ties -> lowest original cell index.  Stackless traversal of the complete heap-indexed tree:
+// descend to the leaf on the query's side, scan its LEAF slots, then climb; at every ancestor
+// reached from its near child the far child is entered iff (q[dim]-split)^2 <= best.  By
+// monotonicity of fp64 subtraction, multiplication and addition, (q[dim]-split)^2 is a lower
+// bound of the COMPUTED squared distance of every centre behind the plane, so pruning with '>'
+// never drops the true fp64 minimum or a tie.  Returns the 0-based device slot, -1 if none.
+__device__ __forceinline__ int nearest_center(const TreeView& t, const double* s_split, const uint8_t* s_dim, double qx,
+                                              double qy, double qz) {
+  double best = __longlong_as_double(0x7ff0000000000000LL);
+  int besti = -1;
+  long long besto = 0x7fffffffffffffffLL;
+  int node = 0;
+  for (;;) {
+    while (node < t.n_internal) {   // descend
+      double s; int k;
+      if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
+      else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
+      const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
+      node = 2 * node + 1 + (qk < s ? 0 : 1);
+    }
+    {   // leaf scan, two batches of four slots (8 independent 16-B loads in flight each)
+      const int base = (node - t.n_internal) * LEAF;
+      const double2* c = reinterpret_cast<const double2*>(t.centers4) + 2 * (size_t)base;
+#pragma unroll
+      for (int h = 0; h < LEAF; h += 4) {
+        double2 a[4], b[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { a[j] = __ldg(c + 2 * (h + j)); b[j] = __ldg(c + 2 * (h + j) + 1); }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const double dx = a[j].x - qx, dy = a[j].y - qy, dz = b[j].x - qz;
+          const double sd = (dx * dx + dy * dy) + dz * dz;
+          if (sd < best) { best = sd; besti = base + h + j; besto = __double_as_longlong(b[j].y); }
+          else if (sd == best && __double_as_longlong(b[j].y) < besto && __double_as_longlong(b[j].y) > 0) {
+            besti = base + h + j; besto = __double_as_longlong(b[j].y);
+          }
+        }
+      }
+    }
+    bool done = false;
+    for (;;) {   // climb
+      if (node == 0) { done = true; break; }
+      const int child = node;
+      node = (node - 1) >> 1;
+      double s; int k;
+      if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
+      else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
+      const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
+      const int near_right = qk < s ? 0 : 1;
+      const int was_right = (child & 1) ? 0 : 1;
+      if (was_right == near_right) {
+        const double d = qk - s;
+        if (!(d * d > best)) { node = 2 * node + 1 + (1 - near_right); break; }
+      }
+    }
+    if (done) break;
+  }
+  return besti;
+}
+
+// iu_get_cell_through_neighbors (:667-725) + get_cell_intersection (:729-764).
+// Cells are 1-based DEVICE ids.  mask = icell_data column (original cell order) or null.
+template <int PPC>
+__device__ __forceinline__ void walk_ray(const double* __restrict__ rec, V3 r0, V3 r1, int ic0, int max_steps,
+                                         const int32_t* __restrict__ mask, int& ic1, V3& r_p, int& n_steps, int& status,
+                                         bool& early) {
+  using L = RecLayout<PPC>;
+  const V3 dvec = r1 - r0;
+  double distance_left = norm2_3(dvec);
+  status = 0;
+  early = false;
+  ic1 = ic0;
+  if (distance_left < TINY_DISTANCE) { early = true; return; }   // :689-692
+  const V3 u{dvec.x / distance_left, dvec.y / distance_left, dvec.z / distance_left};   // :694
+  r_p = r0;
+  int mask0 = 0;
+  if (mask) mask0 = __ldg(mask + (__ldg(reinterpret_cast<const int32_t*>(rec + (size_t)(ic0 - 1) * L::STRIDE) + L::ORG_I) - 1));
+  for (n_steps = 1; n_steps <= max_steps; ++n_steps) {
+    const double* R = rec + (size_t)(ic1 - 1) * L::STRIDE;
+    double face_distance = HUGE_DISTANCE;
+    int i_face = -1;
+#pragma unroll
+    for (int k = 0; k < PPC; ++k) {
+      const V3 fn = ld3(R + L::NRM + 3 * k);
+      const double pdn = dot3(u, fn);
+      if (pdn > 0) {
+        const V3 rf = ld3(R + L::PTS + 3 * k);
+        const double dist = dot3(rf - r_p, fn) / pdn;
+        if (dist < face_distance) { face_distance = dist; i_face = k; }
+      }
+    }
+    r_p = {r_p.x + face_distance * u.x, r_p.y + face_distance * u.y, r_p.z + face_distance * u.z};   // :762
+    distance_left = distance_left - face_distance;
+    if (distance_left > 0) {
+      ic1 = __ldg(reinterpret_cast<const int32_t*>(R) + L::NBR_I + i_face);
+      if (ic1 < 1) { status = -1; break; }
+      if (mask) {
+        const int o1 = __ldg(reinterpret_cast<const int32_t*>(rec + (size_t)(ic1 - 1) * L::STRIDE) + L::ORG_I);
+        if (mask0 != __ldg(mask + (o1 - 1))) { status = 1; break; }
+      }
+    } else {
+      break;
+    }
+  }
+}
+
+// interpolate_triangle (:529-551), interpolate_quad (:591-641), interpolate_tetrahedron (:555-586):
+// computes the per-vertex weights once, then applies them to every requested variable.
+template <int CT> struct Weights;
+template <> struct Weights<IU_TETRA_CT> {
+  double w[4], inv;
+  __device__ __forceinline__ void setup(const V3* p, double vol, V3 r) {
+    const V3 v1r = r - p[0], v2r = r - p[1];
+    const V3 v12 = p[1] - p[0], v13 = p[2] - p[0], v14 = p[3] - p[0], v23 = p[2] - p[1], v24 = p[3] - p[1];
+    w[0] = stp(v2r, v24, v23);
+    w[1] = stp(v1r, v13, v14);
+    w[2] = stp(v1r, v14, v12);
+    w[3] = stp(v1r, v12, v13);
+    inv = 1 / (6 * vol);
+  }
+  __device__ __forceinline__ double apply(const double* d) const {
+    return (((d[0] * w[0] + d[1] * w[1]) + d[2] * w[2]) + d[3] * w[3]) * inv;
+  }
+};
+template <> struct Weights<IU_TRIANGLE_CT> {
+  double w[3], inv;
+  __device__ __forceinline__ void setup(const V3* p, double area, V3 r) {
+    w[0] = 0.5 * norm2_3(cross(r - p[1], r - p[2]));
+    w[1] = 0.5 * norm2_3(cross(r - p[2], r - p[0]));
+    w[2] = 0.5 * norm2_3(cross(r - p[0], r - p[1]));
+    inv = 1 / area;
+  }
+  __device__ __forceinline__ double apply(const double* d) const {
+    return ((d[0] * w[0] + d[1] * w[1]) + d[2] * w[2]) * inv;
+  }
+};
+template <> struct Weights<IU_QUAD_CT> {
+  double c1, c2;
+  __device__ __forceinline__ void setup(const V3* p, double, V3 r) {
+    const double tiny_value = 1e-20;
+    const V3 q = r - p[0];
+    const V3 b1 = p[1] - p[0];
+    const V3 b2 = p[3] - p[0];
+    const V3 b3 = ((p[0] - p[1]) - p[3]) + p[2];
+    const double A = cross_z(b2, b3);
+    const double B = cross_z(b3, q) - cross_z(b1, b2);
+    const double C = cross_z(b1, q);
+    const double discrim = B * B - 4 * A * C;
+    if (fabs(A) < tiny_value) c2 = -C / B;
+    else c2 = 0.5 * (-B - sqrt(discrim)) / A;
+    const double dx = b1.x + c2 * b3.x, dy = b1.y + c2 * b3.y, dz = b1.z + c2 * b3.z;
+    // maxloc(abs(denom)): first maximum
+    int dim = 0; double dm = fabs(dx);
+    if (fabs(dy) > dm) { dim = 1; dm = fabs(dy); }
+    if (fabs(dz) > dm) { dim = 2; }
+    const double qd = dim == 0 ? q.x : (dim == 1 ? q.y : q.z);
+    const double b2d = dim == 0 ? b2.x : (dim == 1 ? b2.y : b2.z);
+    const double dd = dim == 0 ? dx : (dim == 1 ? dy : dz);
+    c1 = (qd - b2d * c2) / dd;
+  }
+  __device__ __forceinline__ double apply(const double* d) const {
+    const double t1 = d[0] * (1 - c1) + d[1] * c1;
+    const double t2 = d[3] * (1 - c1) + d[2] * c1;
+    return t1 * (1 - c2) + t2 * c2;
+  }
+};
+
+struct QueryKernelParams {
+  TreeView tree;
+  const double* rec;
+  const int32_t* dev_of_orig;
+  const int32_t* orig_of_dev;
+  const double* pd;
+  const double* cd;
+  const int32_t* icd;
+  unsigned long long* counters;
+  const double* r;
+  const uint32_t* perm;
+  int32_t* i_cell;
+  double* out_f64;
+  int32_t* out_i32;
+  int64_t n;
+  int n_cells;
+  int pd_stride;
+  int n_vars;
+  int max_steps;
+  int ivars[MAX_VARS];
+};
+
+// THE hot kernel.  Persistent CTAs (grid = SMs x resident CTAs); the top tree levels live in
+// shared memory; one query per thread, processed in Morton order through `perm`.
+template <int CT, int MODE, int NV>
+__global__ void __launch_bounds__(QUERY_THREADS) k_query(const QueryKernelParams P) {
+  constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
+  using L = RecLayout<PPC>;
+  __shared__ double s_split[MAX_SM_NODES];
+  __shared__ uint8_t s_dim[MAX_SM_NODES + 1];
+  if (MODE != QM_INTERP_ICELL) {
+    for (int i = threadIdx.x; i < P.tree.n_sm_nodes; i += blockDim.x) { s_split[i] = P.tree.split[i]; s_dim[i] = P.tree.sdim[i]; }
+    __syncthreads();
+  }
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < P.n; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = P.perm ? (int64_t)__ldg(P.perm + t) : t;
+    const double qx = __ldg(P.r + 3 * i), qy = __ldg(P.r + 3 * i + 1), qz = __ldg(P.r + 3 * i + 2);
+    int ic;   // 1-based device id of the containing cell, or <= 0
+    if (MODE == QM_NEAREST) {
+      const int slot = nearest_center(P.tree, s_split, s_dim, qx, qy, qz);
+      P.out_i32[i] = slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0;
+      continue;
+    } else if (MODE == QM_INTERP_ICELL) {
+      const int h = P.i_cell[i];
+      if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }
+      if (h < 1) continue;
+      ic = __ldg(P.dev_of_orig + h);
+    } else {
+      const int h = P.i_cell[i];
+      if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }   // error stop, :490
+      int start;
+      if (h < 1) {                                                                      // :422-423
+        const int slot = nearest_center(P.tree, s_split, s_dim, qx, qy, qz);
+        if (slot < 0) { P.i_cell[i] = 0; atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
+        start = slot + 1;
+      } else {
+        start = __ldg(P.dev_of_orig + h);                                               // :424-426
+      }
+      const double* c4 = P.tree.centers4 + 4 * (size_t)(start - 1);
+      const V3 r0{__ldg(c4), __ldg(c4 + 1), __ldg(c4 + 2)};                             // :429
+      V3 r_p; int n_steps = 0, status; bool early;
+      walk_ray<PPC>(P.rec, r0, V3{qx, qy, qz}, start, P.max_steps, nullptr, ic, r_p, n_steps, status, early);
+      if (!early && n_steps > P.max_steps) {
+        ic = IU_WALK_LIMIT;
+        atomicAdd(P.counters + CNT_WALK_LIMIT, 1ULL);
+      }
+      if (ic < 1) { P.i_cell[i] = ic; atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }   // :492
+    }
+    const double* R = P.rec + (size_t)(ic - 1) * L::STRIDE;
+    const int32_t* RI = reinterpret_cast<const int32_t*>(R);
+    const int orig = __ldg(RI + L::ORG_I);
+    if (MODE != QM_INTERP_ICELL) P.i_cell[i] = orig;
+    if (MODE == QM_CELL_F64) {
+      P.out_f64[i] = __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1));          // :447
+    } else if (MODE == QM_CELL_I32) {
+      P.out_i32[i] = __ldg(P.icd + (size_t)P.ivars[0] * P.n_cells + (orig - 1));         // :461
+    } else if (MODE == QM_INTERP || MODE == QM_INTERP_ICELL) {                           // :498-527
+      V3 p[PPC];
+      int pid[PPC];
+#pragma unroll
+      for (int k = 0; k < PPC; ++k) { p[k] = ld3(R + L::PTS + 3 * k); pid[k] = __ldg(RI + L::CEL_I + k); }
+      Weights<CT> W;
+      W.setup(p, __ldg(R + L::VOL), V3{qx, qy, qz});
+      double* out = P.out_f64 + (size_t)i * P.n_vars;
+      if (NV > 0) {
+        double res[NV];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          double d[4];
+#pragma unroll
+          for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
+          res[v] = W.apply(d);
+        }
+        if (NV % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+#pragma unroll
+          for (int v = 0; v < NV; v += 2) *reinterpret_cast<double2*>(out + v) = make_double2(res[v], res[v + 1]);
+        } else {
+#pragma unroll
+          for (int v = 0; v < NV; ++v) out[v] = res[v];
+        }
+      } else {
+        for (int v = 0; v < P.n_vars; ++v) {
+          double d[4];
+#pragma unroll
+          for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
+          out[v] = W.apply(d);
+        }
+      }
+    }
+  }
+}
+
+template <int PPC>
+__global__ void __launch_bounds__(QUERY_THREADS) k_walk(const double* __restrict__ rec, const int32_t* __restrict__ dev_of_orig,
+                                                        const int32_t* __restrict__ orig_of_dev, const int32_t* __restrict__ mask,
+                                                        int n_cells, unsigned long long* counters, WalkArgs a) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int h = a.ic0[i];
+    if (h < 1 || h > n_cells) { atomicAdd(counters + CNT_HINT_ERROR, 1ULL); continue; }
+    const V3 r0 = ld3(a.r0 + 3 * i), r1 = ld3(a.r1 + 3 * i);
+    int ic1, n_steps = 0, status; V3 r_p; bool early;
+    walk_ray<PPC>(rec, r0, r1, __ldg(dev_of_orig + h), a.max_steps, mask, ic1, r_p, n_steps, status, early);
+    a.ic1[i] = ic1 >= 1 ? __ldg(orig_of_dev + (ic1 - 1)) : ic1;
+    a.status[i] = status;
+    if (!early) {   // r_p / n_steps undefined on the early return, :689-692
+      a.r_p[3 * i] = r_p.x; a.r_p[3 * i + 1] = r_p.y; a.r_p[3 * i + 2] = r_p.z;
+      a.n_steps[i] = n_steps;
+    }
+  }
+}
+
+int query_grid_blocks(const void* kernel) {
+  static int n_sm = 0;
+  if (n_sm == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    if (n_sm <= 0) n_sm = 148;
+  }
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QUERY_THREADS, 0);
+  if (per_sm < 1) per_sm = 1;
+  return n_sm * per_sm;
+}
+
+template <int CT, int MODE, int NV>
+void launch_query_inst(const QueryKernelParams& P, cudaStream_t s) {
+  static int blocks = 0;
+  if (blocks == 0) blocks = query_grid_blocks((const void*)k_query<CT, MODE, NV>);
+  int64_t need = (P.n + QUERY_THREADS - 1) / QUERY_THREADS;
+  int g = (int)(need < blocks ? need : blocks);
+  k_query<CT, MODE, NV><<<g, QUERY_THREADS, 0, s>>>(P);
+}
+
+template <int CT>
+void launch_query_ct(int mode, const QueryKernelParams& P, cudaStream_t s) {
+  switch (mode) {
+    case QM_NEAREST: launch_query_inst<CT, QM_NEAREST, 0>(P, s); break;
+    case QM_CELL: launch_query_inst<CT, QM_CELL, 0>(P, s); break;
+    case QM_CELL_F64: launch_query_inst<CT, QM_CELL_F64, 0>(P, s); break;
+    case QM_CELL_I32: launch_query_inst<CT, QM_CELL_I32, 0>(P, s); break;
+    case QM_INTERP:
+      switch (P.n_vars) {
+        case 1: launch_query_inst<CT, QM_INTERP, 1>(P, s); break;
+        case 2: launch_query_inst<CT, QM_INTERP, 2>(P, s); break;
+        case 3: launch_query_inst<CT, QM_INTERP, 3>(P, s); break;
+        case 4: launch_query_inst<CT, QM_INTERP, 4>(P, s); break;
+        case 8: launch_query_inst<CT, QM_INTERP, 8>(P, s); break;
+        default: launch_query_inst<CT, QM_INTERP, 0>(P, s); break;
+      }
+      break;
+    case QM_INTERP_ICELL:
+      switch (P.n_vars) {
+        case 1: launch_query_inst<CT, QM_INTERP_ICELL, 1>(P, s); break;
+        case 2: launch_query_inst<CT, QM_INTERP_ICELL, 2>(P, s); break;
+        case 3: launch_query_inst<CT, QM_INTERP_ICELL, 3>(P, s); break;
+        case 4: launch_query_inst<CT, QM_INTERP_ICELL, 4>(P, s); break;
+        default: launch_query_inst<CT, QM_INTERP_ICELL, 0>(P, s); break;
+      }
+      break;
+  }
+}
+
+inline int blocks_for(int64_t n, int threads) { return (int)((n + threads - 1) / threads); }
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+int launch_cell_centers(const DeviceGrid& g, const double* points, const int32_t* cells, double* centers, cudaStream_t s) {
+  if (g.n_cells == 0) return 0;
+  const int b = blocks_for(g.n_cells, 256);
+  if (g.ppc == 3) k_cell_centers<3><<<b, 256, 0, s>>>(g.n_cells, points, cells, centers);
+  else k_cell_centers<4><<<b, 256, 0, s>>>(g.n_cells, points, cells, centers);
+  return 1;
+}
+
+int launch_build_records(const DeviceGrid& g, const double* points, const int32_t* cells, const int32_t* neighbors,
+                         const double* centers, cudaStream_t s) {
+  const int n_slots = g.n_leaves * LEAF;
+  if (n_slots == 0) return 0;
+  const int b = blocks_for(n_slots, 128);
+  k_fill_dev_of_orig<<<blocks_for(n_slots, 256), 256, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig);
+  if (g.cell_type == IU_TRIANGLE_CT)
+    k_build_records<3, IU_TRIANGLE_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4);
+  else if (g.cell_type == IU_QUAD_CT)
+    k_build_records<4, IU_QUAD_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4);
+  else
+    k_build_records<4, IU_TETRA_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4);
+  return 2;
+}
+
+int launch_export_geometry(const DeviceGrid& g, double* cell_points, double* normals, double* volume, double* centers,
+                           cudaStream_t s) {
+  const int n_slots = g.n_leaves * LEAF;
+  if (n_slots == 0) return 0;
+  const int b = blocks_for(n_slots, 128);
+  if (g.ppc == 3) k_export_geometry<3><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.rec, g.centers4, cell_points, normals, volume, centers);
+  else k_export_geometry<4><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.rec, g.centers4, cell_points, normals, volume, centers);
+  return 1;
+}
+
+int launch_pack_point_data(const DeviceGrid& g, const double* cols, int col0, int n_cols, cudaStream_t s) {
+  const int64_t n = (int64_t)g.n_points * n_cols;
+  if (n == 0) return 0;
+  k_pack_point_data<<<blocks_for(n, 256), 256, 0, s>>>(g.n_points, n_cols, col0, g.pd_stride, cols, g.pd);
+  return 1;
+}
+
+int launch_repack_point_data(const double* old_pd, int old_stride, double* new_pd, int new_stride, int n_cols, int n_points,
+                             cudaStream_t s) {
+  const int64_t n = (int64_t)n_points * new_stride;
+  if (n == 0) return 0;
+  k_repack_point_data<<<blocks_for(n, 256), 256, 0, s>>>(n_points, n_cols, old_stride, new_stride, old_pd, new_pd);
+  return 1;
+}
+
+int launch_generate_queries(int64_t n, int64_t first, uint64_t seed, const double lo[3], const double hi[3], double* r,
+                            cudaStream_t s) {
+  if (n == 0) return 0;
+  k_generate_queries<<<blocks_for(3 * n, 256), 256, 0, s>>>(n, first, seed, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2], r);
+  return 1;
+}
+
+int launch_merge_rows(int64_t n, int row_bytes, const int32_t* i_cell, const void* src, void* dst, cudaStream_t s) {
+  if (n == 0) return 0;
+  const int words = row_bytes / 4;
+  k_merge_rows<<<blocks_for(n * words, 256), 256, 0, s>>>(n, words, i_cell, (const uint32_t*)src, (uint32_t*)dst);
+  return 1;
+}
+
+// bits per dimension of the Morton key: about one key cell per mesh cell
+static void morton_bits(const DeviceGrid& g, int& bits, int& planar) {
+  planar = (g.rmax[2] - g.rmin[2]) == 0.0 ? 1 : 0;
+  double lg = 0;
+  for (int64_t c = 1; c < g.n_cells; c <<= 1) lg += 1;
+  if (planar) { bits = (int)((lg + 1) / 2); bits = bits < 1 ? 1 : (bits > 15 ? 15 : bits); }
+  else { bits = (int)((lg + 2) / 3); bits = bits < 1 ? 1 : (bits > 10 ? 10 : bits); }
+}
+
+int morton_end_bit(const DeviceGrid& g) {
+  int bits, planar;
+  morton_bits(g, bits, planar);
+  return planar ? 2 * bits : 3 * bits;
+}
+
+size_t sort_temp_bytes(int64_t n, int end_bit) {
+  size_t bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr,
+                                  (uint32_t*)nullptr, n, 0, end_bit);
+  return bytes;
+}
+
+int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t* keys, uint32_t* keys_alt, uint32_t* idx,
+                       uint32_t* idx_alt, void* temp, size_t temp_bytes, int* end_bit_out, cudaStream_t s) {
+  int bits, planar;
+  morton_bits(g, bits, planar);
+  const double nb = (double)(1u << bits);
+  double sc[3];
+  for (int k = 0; k < 3; ++k) { const double ext = g.rmax[k] - g.rmin[k]; sc[k] = ext > 0 ? nb / ext : 0.0; }
+  k_morton_keys<<<blocks_for(n, 256), 256, 0, s>>>(n, r, g.rmin[0], g.rmin[1], g.rmin[2], sc[0], sc[1], sc[2], bits, planar, keys, idx);
+  const int end_bit = planar ? 2 * bits : 3 * bits;
+  cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const uint32_t*)keys, keys_alt, (const uint32_t*)idx, idx_alt, n, 0, end_bit, s);
+  if (end_bit_out) *end_bit_out = end_bit;
+  // cub one-sweep: 1 histogram + 1 scan-ish + ceil(end_bit/8) passes; counted conservatively
+  return 1 + 2 + (end_bit + 7) / 8;
+}
+
+int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
+  if (a.n == 0) return 0;
+  QueryKernelParams P;
+  P.tree = TreeView{g.split, g.sdim, g.centers4, g.n_internal, g.n_sm_nodes};
+  P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
+  P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
+  P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
+  P.n = a.n; P.n_cells = g.n_cells; P.pd_stride = g.pd_stride; P.n_vars = a.n_vars; P.max_steps = a.max_steps;
+  for (int v = 0; v < MAX_VARS; ++v) P.ivars[v] = a.ivars[v];
+  if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, s);
+  else if (g.cell_type == IU_QUAD_CT) launch_query_ct<IU_QUAD_CT>(a.mode, P, s);
+  else launch_query_ct<IU_TETRA_CT>(a.mode, P, s);
+  return 1;
+}
+
+int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s) {
+  if (a.n == 0) return 0;
+  const int32_t* mask = a.mask_col >= 0 ? g.icd + (size_t)a.mask_col * g.n_cells : nullptr;
+  const int64_t need = (a.n + QUERY_THREADS - 1) / QUERY_THREADS;
+  const int b = (int)(need < 148 * 8 ? need : 148 * 8);
+  if (g.ppc == 3) k_walk<3><<<b, QUERY_THREADS, 0, s>>>(g.rec, g.dev_of_orig, g.orig_of_dev, mask, g.n_cells, g.counters, a);
+  else k_walk<4><<<b, QUERY_THREADS, 0, s>>>(g.rec, g.dev_of_orig, g.orig_of_dev, mask, g.n_cells, g.counters, a);
+  return 1;
+}
+
+}  // namespace iu
