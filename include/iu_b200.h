@@ -61,6 +61,7 @@ extern "C" {
 #define IU_B200_STAT_WORKSPACE_BYTES 3
 #define IU_B200_STAT_MESH_BYTES 4
 #define IU_B200_STAT_TREE_DEPTH 5
+#define IU_B200_STAT_NOT_FOUND 6       /* queries that ended with i_cell <= 0 */
 #define IU_B200_N_STATS 8
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */
@@ -121,7 +122,8 @@ int iu_b200_add_icell_data(iu_b200_grid* grid, const char* name, int* i_var);
 
 /* Refresh device columns after the caller changed them on the host (the reference's callers
  * write ug%point_data directly, test_tetra.f90:38-40, test_trace_field.f90:20-23).
- * data = (n_points|n_cells, n_cols) column-major host array for columns col0 .. col0+n_cols-1. */
+ * data = (n_points|n_cells, n_cols) column-major host array for the 1-based columns
+ * col0 .. col0+n_cols-1. */
 int iu_b200_update_point_data(iu_b200_grid* grid, int col0, int n_cols, const double* data);
 int iu_b200_update_cell_data(iu_b200_grid* grid, int col0, int n_cols, const double* data);
 int iu_b200_update_icell_data(iu_b200_grid* grid, int col0, int n_cols, const int32_t* data);

@@ -1,0 +1,971 @@
+// api.cu -- the C ABI of libiu_b200.so (include/iu_b200.h): grid lifecycle, the device-buffer
+// entry points (sub-batching + optional Morton sort around the kernels of kernels.cu) and the
+// host-buffer entry points (three-slot H2D / compute / D2H pipeline on three streams).
+//
+// There is no CPU fallback anywhere in this file: every entry point needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "../../include/iu_b200.h"
+#include "device.h"
+
+namespace iu {
+
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+
+namespace {
+
+struct CudaFail {
+  int code;
+};
+
+#define CU(expr)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e__ = (expr);                                                                            \
+    if (e__ != cudaSuccess) {                                                                            \
+      set_error(std::string(#expr) + ": " + cudaGetErrorString(e__));                                    \
+      throw CudaFail{e__ == cudaErrorMemoryAllocation ? IU_B200_ENOMEM : IU_B200_ECUDA};                 \
+    }                                                                                                    \
+  } while (0)
+
+template <class T>
+struct DevBuf {   // RAII device buffer
+  T* p = nullptr;
+  size_t n = 0;
+  DevBuf() = default;
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  void alloc(size_t count) {
+    release();
+    if (count == 0) return;
+    CU(cudaMalloc((void**)&p, count * sizeof(T)));
+    n = count;
+  }
+  void ensure(size_t count) {
+    if (count > n) alloc(count);
+  }
+  T* take() {
+    T* q = p;
+    p = nullptr;
+    n = 0;
+    return q;
+  }
+};
+
+constexpr int N_SLOTS = 3;   // host-API pipeline depth
+
+struct Slot {
+  DevBuf<double> r, r1, out_f64;
+  DevBuf<int32_t> i_a, i_b, i_c, i_d;
+  cudaEvent_t in_done = nullptr, comp_done = nullptr, out_done = nullptr;
+};
+
+}  // namespace
+}  // namespace iu
+
+using namespace iu;
+
+struct iu_b200_grid {
+  int device = 0;
+  DeviceGrid dg;
+  std::vector<std::string> point_names, cell_names, icell_names;
+  // options
+  int sort_mode = 2;
+  int64_t max_walk_steps = 1 << 20;
+  int64_t host_chunk = 1 << 22;
+  int64_t dev_batch = 1 << 26;
+  // stats
+  int64_t n_launches = 0, n_queries = 0;
+  size_t mesh_bytes = 0;
+  int tree_depth = 0;
+  // sort workspace (device API and host pipeline share it: all compute is stream-ordered by the caller)
+  DevBuf<uint32_t> keys, keys_alt, idx, idx_alt;
+  DevBuf<char> sort_temp;
+  // host pipeline
+  cudaStream_t s_in = nullptr, s_comp = nullptr, s_out = nullptr;
+  Slot slot[N_SLOTS];
+  unsigned long long* h_counters = nullptr;   // pinned, N_SLOTS x CNT_N snapshots
+  void* h_stage = nullptr;                     // pinned staging for the rare "merge" path
+  size_t h_stage_bytes = 0;
+  unsigned long long seen[CNT_N] = {0, 0, 0, 0};   // counter values already accounted for
+  std::mutex mu;   // one batch call at a time per grid (workspaces are per grid)
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+size_t workspace_bytes(const iu_b200_grid* g) {
+  size_t b = (g->keys.n + g->keys_alt.n + g->idx.n + g->idx_alt.n) * 4 + g->sort_temp.n + g->h_stage_bytes;
+  for (const Slot& s : g->slot)
+    b += (s.r.n + s.r1.n + s.out_f64.n) * 8 + (s.i_a.n + s.i_b.n + s.i_c.n + s.i_d.n) * 4;
+  return b;
+}
+
+void free_device_grid(DeviceGrid& d) {
+  cudaFree(d.split); cudaFree(d.sdim); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
+  cudaFree(d.orig_of_dev); cudaFree(d.pd); cudaFree(d.cd); cudaFree(d.icd); cudaFree(d.counters);
+  d = DeviceGrid();
+}
+
+int round_up_stride(int n_cols) {
+  // point-major rows: keep rows 16-byte aligned and, from 3 columns on, 32-byte (sector) aligned
+  if (n_cols <= 1) return 1;
+  if (n_cols == 2) return 2;
+  return (n_cols + 3) / 4 * 4;
+}
+
+template <class F>
+int guarded(F&& f) {
+  try {
+    return f();
+  } catch (const CudaFail& e) {
+    return e.code;
+  } catch (const std::bad_alloc&) {
+    set_error("out of host memory");
+    return IU_B200_ENOMEM;
+  }
+}
+
+bool check_device_available() {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    set_error(std::string("no usable CUDA device (") + (e != cudaSuccess ? cudaGetErrorString(e) : "count = 0") +
+              "); libiu_b200 has no CPU fallback");
+    return false;
+  }
+  return true;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// lifecycle
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+int create_from_arrays(int cell_type, int n_points, int n_cells, const double* points, const int32_t* cells,
+                       const int32_t* neighbors, int n_pd, const double* pd, int n_cd, const double* cd, int n_icd,
+                       const int32_t* icd, int device, iu_b200_grid** out) {
+  if (!out) { set_error("grid pointer is null"); return IU_B200_EINVAL; }
+  *out = nullptr;
+  if (cell_type < 1 || cell_type > 3) { set_error("unknown cell type"); return IU_B200_EINVAL; }
+  if (n_points < 1 || n_cells < 1 || !points || !cells || !neighbors) { set_error("empty or missing mesh arrays"); return IU_B200_EINVAL; }
+  if (n_pd < 0 || n_cd < 0 || n_icd < 0 || (n_pd > 0 && !pd) || (n_cd > 0 && !cd) || (n_icd > 0 && !icd)) {
+    set_error("inconsistent data tables");
+    return IU_B200_EINVAL;
+  }
+  const int ppc = cell_type == IU_TRIANGLE_CT ? 3 : 4;
+  for (size_t i = 0; i < (size_t)n_cells * ppc; ++i) {
+    if (cells[i] < 1 || cells[i] > n_points) { set_error("cells: point index outside 1..n_points"); return IU_B200_EINVAL; }
+    if (neighbors[i] > n_cells) { set_error("neighbors: cell index above n_cells"); return IU_B200_EINVAL; }
+  }
+  if (!check_device_available()) return IU_B200_ECUDA;
+  if (device < 0) cudaGetDevice(&device);
+  iu_b200_grid* g = new iu_b200_grid();
+  g->device = device;
+  int rc = guarded([&]() {
+    DeviceGuard guard(device);
+    cudaStream_t s = nullptr;
+    DeviceGrid& d = g->dg;
+    d.cell_type = cell_type; d.ppc = ppc; d.n_cells = n_cells; d.n_points = n_points;
+    for (int k = 0; k < 3; ++k) { d.rmin[k] = points[k]; d.rmax[k] = points[k]; }   // :867-868
+    for (size_t i = 1; i < (size_t)n_points; ++i)
+      for (int k = 0; k < 3; ++k) {
+        const double v = points[3 * i + k];
+        d.rmin[k] = v < d.rmin[k] ? v : d.rmin[k];
+        d.rmax[k] = v > d.rmax[k] ? v : d.rmax[k];
+      }
+    // raw mesh -> device (temporary; only the records survive)
+    DevBuf<double> d_points, d_centers;
+    DevBuf<int32_t> d_cells, d_neigh;
+    d_points.alloc((size_t)3 * n_points);
+    d_cells.alloc((size_t)ppc * n_cells);
+    d_neigh.alloc((size_t)ppc * n_cells);
+    d_centers.alloc((size_t)3 * n_cells);
+    CU(cudaMemcpyAsync(d_points.p, points, d_points.n * 8, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_cells.p, cells, d_cells.n * 4, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(d_neigh.p, neighbors, d_neigh.n * 4, cudaMemcpyHostToDevice, s));
+    // cell centres with the reference's arithmetic (build_kdtree :251-262), then the tree on the host
+    g->n_launches += launch_cell_centers(d, d_points.p, d_cells.p, d_centers.p, s);
+    std::vector<double> h_centers((size_t)3 * n_cells);
+    CU(cudaMemcpyAsync(h_centers.data(), d_centers.p, h_centers.size() * 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    KdTreeHost tree;
+    build_kdtree(h_centers.data(), n_cells, tree);
+    std::vector<double>().swap(h_centers);
+    d.n_leaves = tree.n_leaves;
+    d.n_internal = tree.n_leaves - 1;
+    d.n_sm_nodes = std::min(d.n_internal, 2047);
+    for (int l = 1; l < tree.n_leaves; l <<= 1) ++g->tree_depth;
+    const size_t n_slots = (size_t)tree.n_leaves * LEAF;
+    CU(cudaMalloc((void**)&d.split, std::max<size_t>(1, d.n_internal) * 8));
+    CU(cudaMalloc((void**)&d.sdim, std::max<size_t>(1, d.n_internal)));
+    CU(cudaMalloc((void**)&d.orig_of_dev, n_slots * 4));
+    CU(cudaMalloc((void**)&d.dev_of_orig, ((size_t)n_cells + 1) * 4));
+    CU(cudaMalloc((void**)&d.centers4, n_slots * 32));
+    CU(cudaMalloc((void**)&d.rec, n_slots * rec_stride(ppc) * 8));
+    CU(cudaMalloc((void**)&d.counters, CNT_N * sizeof(unsigned long long)));
+    CU(cudaMemsetAsync(d.counters, 0, CNT_N * sizeof(unsigned long long), s));
+    CU(cudaMemsetAsync(d.dev_of_orig, 0, ((size_t)n_cells + 1) * 4, s));
+    if (d.n_internal > 0) {
+      CU(cudaMemcpyAsync(d.split, tree.split.data(), (size_t)d.n_internal * 8, cudaMemcpyHostToDevice, s));
+      CU(cudaMemcpyAsync(d.sdim, tree.sdim.data(), (size_t)d.n_internal, cudaMemcpyHostToDevice, s));
+    }
+    CU(cudaMemcpyAsync(d.orig_of_dev, tree.orig_of_slot.data(), n_slots * 4, cudaMemcpyHostToDevice, s));
+    g->n_launches += launch_build_records(d, d_points.p, d_cells.p, d_neigh.p, d_centers.p, s);
+    CU(cudaStreamSynchronize(s));
+    // data tables
+    d.n_pd = n_pd;
+    d.pd_stride = round_up_stride(n_pd);
+    if (n_pd > 0) {
+      CU(cudaMalloc((void**)&d.pd, (size_t)n_points * d.pd_stride * 8));
+      CU(cudaMemsetAsync(d.pd, 0, (size_t)n_points * d.pd_stride * 8, s));
+      DevBuf<double> cols;
+      cols.alloc((size_t)n_points * n_pd);
+      CU(cudaMemcpyAsync(cols.p, pd, cols.n * 8, cudaMemcpyHostToDevice, s));
+      g->n_launches += launch_pack_point_data(d, cols.p, 0, n_pd, s);
+      CU(cudaStreamSynchronize(s));
+    }
+    d.n_cd = d.cd_cap = n_cd;
+    if (n_cd > 0) {
+      CU(cudaMalloc((void**)&d.cd, (size_t)n_cells * n_cd * 8));
+      CU(cudaMemcpy(d.cd, cd, (size_t)n_cells * n_cd * 8, cudaMemcpyHostToDevice));
+    }
+    d.n_icd = d.icd_cap = n_icd;
+    if (n_icd > 0) {
+      CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
+      CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
+    }
+    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 9 +
+                    (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
+    CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&g->s_out, cudaStreamNonBlocking));
+    for (Slot& sl : g->slot) {
+      CU(cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&sl.comp_done, cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&sl.out_done, cudaEventDisableTiming));
+    }
+    CU(cudaMallocHost((void**)&g->h_counters, N_SLOTS * CNT_N * sizeof(unsigned long long)));
+    return IU_B200_OK;
+  });
+  if (rc != IU_B200_OK) {
+    iu_b200_grid_destroy(g);
+    return rc;
+  }
+  g->point_names.resize(n_pd);
+  g->cell_names.resize(n_cd);
+  g->icell_names.resize(n_icd);
+  *out = g;
+  return IU_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int iu_b200_version(void) { return 100; }
+
+const char* iu_b200_last_error(void) { return g_error.c_str(); }
+
+int iu_b200_grid_create(const iu_b200_grid_desc* desc, iu_b200_grid** grid) {
+  if (!desc) { set_error("desc is null"); return IU_B200_EINVAL; }
+  return create_from_arrays(desc->cell_type, desc->n_points, desc->n_cells, desc->points, desc->cells, desc->neighbors,
+                            desc->n_point_data, desc->point_data, desc->n_cell_data, desc->cell_data,
+                            desc->n_icell_data, desc->icell_data, desc->device, grid);
+}
+
+int iu_b200_grid_from_binda(const char* filename, double coord_scale_factor, int device, iu_b200_grid** grid) {
+  if (!filename || !grid) { set_error("null argument"); return IU_B200_EINVAL; }
+  HostMesh m;
+  try {
+    if (!read_binda_mesh(filename, coord_scale_factor, m)) return IU_B200_EIO;
+  } catch (const std::bad_alloc&) {
+    set_error("out of host memory");
+    return IU_B200_ENOMEM;
+  }
+  int rc = create_from_arrays(m.cell_type, m.n_points, m.n_cells, m.points.data(), m.cells.data(), m.neighbors.data(),
+                              (int)m.point_names.size(), m.point_data.data(), (int)m.cell_names.size(),
+                              m.cell_data.data(), (int)m.icell_names.size(), m.icell_data.data(), device, grid);
+  if (rc != IU_B200_OK) return rc;
+  (*grid)->point_names = m.point_names;
+  (*grid)->cell_names = m.cell_names;
+  (*grid)->icell_names = m.icell_names;
+  return IU_B200_OK;
+}
+
+int iu_b200_grid_destroy(iu_b200_grid* g) {
+  if (!g) return IU_B200_OK;
+  {
+    DeviceGuard guard(g->device);
+    cudaDeviceSynchronize();
+    free_device_grid(g->dg);
+    for (Slot& sl : g->slot) {
+      if (sl.in_done) cudaEventDestroy(sl.in_done);
+      if (sl.comp_done) cudaEventDestroy(sl.comp_done);
+      if (sl.out_done) cudaEventDestroy(sl.out_done);
+      sl.r.release(); sl.r1.release(); sl.out_f64.release();
+      sl.i_a.release(); sl.i_b.release(); sl.i_c.release(); sl.i_d.release();
+    }
+    g->keys.release(); g->keys_alt.release(); g->idx.release(); g->idx_alt.release(); g->sort_temp.release();
+    if (g->s_in) cudaStreamDestroy(g->s_in);
+    if (g->s_comp) cudaStreamDestroy(g->s_comp);
+    if (g->s_out) cudaStreamDestroy(g->s_out);
+    if (g->h_counters) cudaFreeHost(g->h_counters);
+    if (g->h_stage) cudaFreeHost(g->h_stage);
+  }
+  delete g;
+  return IU_B200_OK;
+}
+
+int iu_b200_grid_info(const iu_b200_grid* g, int32_t info[8]) {
+  if (!g || !info) { set_error("null argument"); return IU_B200_EINVAL; }
+  info[0] = g->dg.cell_type; info[1] = g->dg.n_points; info[2] = g->dg.n_cells; info[3] = g->dg.ppc;
+  info[4] = g->dg.n_pd; info[5] = g->dg.n_cd; info[6] = g->dg.n_icd; info[7] = g->device;
+  return IU_B200_OK;
+}
+
+int iu_b200_grid_bounds(const iu_b200_grid* g, double rmin[3], double rmax[3]) {
+  if (!g || !rmin || !rmax) { set_error("null argument"); return IU_B200_EINVAL; }
+  for (int k = 0; k < 3; ++k) { rmin[k] = g->dg.rmin[k]; rmax[k] = g->dg.rmax[k]; }
+  return IU_B200_OK;
+}
+
+static int find_name(const std::vector<std::string>& names, const char* name) {
+  if (!name) return -1;
+  for (size_t i = 0; i < names.size(); ++i)
+    if (names[i] == name) return (int)i + 1;
+  return -1;
+}
+int iu_b200_get_point_data_index(const iu_b200_grid* g, const char* name) { return g ? find_name(g->point_names, name) : -1; }
+int iu_b200_get_cell_data_index(const iu_b200_grid* g, const char* name) { return g ? find_name(g->cell_names, name) : -1; }
+int iu_b200_get_icell_data_index(const iu_b200_grid* g, const char* name) { return g ? find_name(g->icell_names, name) : -1; }
+const char* iu_b200_point_data_name(const iu_b200_grid* g, int i_var) {
+  if (!g || i_var < 1 || i_var > (int)g->point_names.size()) return nullptr;
+  return g->point_names[i_var - 1].c_str();
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// data columns, options, statistics
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+// grow a column-major (n_rows, n) device table by one zero column
+template <class T>
+void append_zero_column(T*& tab, int& n, int& cap, size_t n_rows) {
+  if (n + 1 > cap) {
+    const int new_cap = std::max(4, cap * 2);
+    T* q = nullptr;
+    CU(cudaMalloc((void**)&q, n_rows * new_cap * sizeof(T)));
+    if (n > 0) CU(cudaMemcpy(q, tab, n_rows * n * sizeof(T), cudaMemcpyDeviceToDevice));
+    cudaFree(tab);
+    tab = q;
+    cap = new_cap;
+  }
+  CU(cudaMemset(tab + n_rows * n, 0, n_rows * sizeof(T)));
+  ++n;
+}
+
+}  // namespace
+
+extern "C" {
+
+int iu_b200_add_point_data(iu_b200_grid* g, const char* name, int* i_var) {
+  if (!g || !name) { set_error("null argument"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    DeviceGrid& d = g->dg;
+    CU(cudaDeviceSynchronize());
+    if (d.n_pd + 1 > d.pd_stride || !d.pd) {
+      const int ns = round_up_stride(d.n_pd + 1);
+      double* q = nullptr;
+      CU(cudaMalloc((void**)&q, (size_t)d.n_points * ns * 8));
+      if (d.pd) g->n_launches += launch_repack_point_data(d.pd, d.pd_stride, q, ns, d.n_pd, d.n_points, nullptr);
+      else CU(cudaMemset(q, 0, (size_t)d.n_points * ns * 8));
+      CU(cudaDeviceSynchronize());
+      cudaFree(d.pd);
+      d.pd = q;
+      d.pd_stride = ns;
+    } else {
+      // the padding column may hold stale values of a column written before: zero it
+      std::vector<double> z((size_t)d.n_points, 0.0);
+      DevBuf<double> col;
+      col.alloc(z.size());
+      CU(cudaMemcpy(col.p, z.data(), z.size() * 8, cudaMemcpyHostToDevice));
+      g->n_launches += launch_pack_point_data(d, col.p, d.n_pd, 1, nullptr);
+      CU(cudaDeviceSynchronize());
+    }
+    ++d.n_pd;
+    g->point_names.push_back(name);
+    if (i_var) *i_var = d.n_pd;
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_add_cell_data(iu_b200_grid* g, const char* name, int* i_var) {
+  if (!g || !name) { set_error("null argument"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    CU(cudaDeviceSynchronize());
+    append_zero_column(g->dg.cd, g->dg.n_cd, g->dg.cd_cap, (size_t)g->dg.n_cells);
+    g->cell_names.push_back(name);
+    if (i_var) *i_var = g->dg.n_cd;
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_add_icell_data(iu_b200_grid* g, const char* name, int* i_var) {
+  if (!g || !name) { set_error("null argument"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    CU(cudaDeviceSynchronize());
+    append_zero_column(g->dg.icd, g->dg.n_icd, g->dg.icd_cap, (size_t)g->dg.n_cells);
+    g->icell_names.push_back(name);
+    if (i_var) *i_var = g->dg.n_icd;
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_update_point_data(iu_b200_grid* g, int col0, int n_cols, const double* data) {
+  if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
+  if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_pd) { set_error("point_data column range outside 1..n_point_data"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    DevBuf<double> cols;
+    cols.alloc((size_t)g->dg.n_points * n_cols);
+    CU(cudaMemcpy(cols.p, data, cols.n * 8, cudaMemcpyHostToDevice));
+    g->n_launches += launch_pack_point_data(g->dg, cols.p, col0 - 1, n_cols, nullptr);
+    CU(cudaDeviceSynchronize());
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_update_cell_data(iu_b200_grid* g, int col0, int n_cols, const double* data) {
+  if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
+  if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_cd) { set_error("cell_data column range outside 1..n_cell_data"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t nc = (size_t)g->dg.n_cells;
+    CU(cudaMemcpy(g->dg.cd + nc * (col0 - 1), data, nc * n_cols * 8, cudaMemcpyHostToDevice));
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_update_icell_data(iu_b200_grid* g, int col0, int n_cols, const int32_t* data) {
+  if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
+  if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_icd) { set_error("icell_data column range outside 1..n_icell_data"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t nc = (size_t)g->dg.n_cells;
+    CU(cudaMemcpy(g->dg.icd + nc * (col0 - 1), data, nc * n_cols * 4, cudaMemcpyHostToDevice));
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_set_option(iu_b200_grid* g, int option, int64_t value) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  switch (option) {
+    case IU_B200_OPT_SORT_QUERIES:
+      if (value < 0 || value > 2) break;
+      g->sort_mode = (int)value;
+      return IU_B200_OK;
+    case IU_B200_OPT_MAX_WALK_STEPS:
+      if (value < 1 || value > 0x7ffffffe) break;
+      g->max_walk_steps = value;
+      return IU_B200_OK;
+    case IU_B200_OPT_HOST_CHUNK:
+      if (value < 1 || value > (1LL << 30)) break;
+      g->host_chunk = value;
+      return IU_B200_OK;
+    case IU_B200_OPT_DEV_BATCH:
+      if (value < 1 || value > (1LL << 31)) break;
+      g->dev_batch = value;
+      return IU_B200_OK;
+    default:
+      set_error("unknown option");
+      return IU_B200_EINVAL;
+  }
+  set_error("option value out of range");
+  return IU_B200_EINVAL;
+}
+
+int iu_b200_get_stats(const iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
+  if (!g || !stats) { set_error("null argument"); return IU_B200_EINVAL; }
+  for (int i = 0; i < IU_B200_N_STATS; ++i) stats[i] = 0;
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    unsigned long long c[CNT_N];
+    CU(cudaMemcpy(c, g->dg.counters, sizeof(c), cudaMemcpyDeviceToHost));
+    stats[IU_B200_STAT_KERNEL_LAUNCHES] = g->n_launches;
+    stats[IU_B200_STAT_WALK_LIMIT_HITS] = (int64_t)c[CNT_WALK_LIMIT];
+    stats[IU_B200_STAT_QUERIES] = g->n_queries;
+    stats[IU_B200_STAT_WORKSPACE_BYTES] = (int64_t)workspace_bytes(g);
+    stats[IU_B200_STAT_MESH_BYTES] = (int64_t)g->mesh_bytes;
+    stats[IU_B200_STAT_TREE_DEPTH] = g->tree_depth;
+    stats[IU_B200_STAT_NOT_FOUND] = (int64_t)c[CNT_NOT_FOUND];
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_reset_stats(iu_b200_grid* g) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    CU(cudaDeviceSynchronize());
+    unsigned long long c[CNT_N];
+    CU(cudaMemcpy(c, g->dg.counters, sizeof(c), cudaMemcpyDeviceToHost));
+    c[CNT_WALK_LIMIT] = 0;
+    c[CNT_NOT_FOUND] = 0;
+    c[CNT_EARLY] = 0;   // the hint-error counter is kept: iu_b200_check_dev compares it with `seen`
+    CU(cudaMemcpy(g->dg.counters, c, sizeof(c), cudaMemcpyHostToDevice));
+    for (int i = 0; i < CNT_N; ++i) g->seen[i] = c[i];
+    g->n_launches = 0;
+    g->n_queries = 0;
+    return IU_B200_OK;
+  });
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// the hot path on device buffers
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+bool want_sort(const iu_b200_grid* g, int mode, int64_t m) {
+  if (mode == QM_INTERP_ICELL) return false;
+  if (g->sort_mode == 0) return false;
+  if (g->sort_mode == 1) return m > 1;
+  return m >= (1 << 15) && g->dg.n_cells >= (1 << 12);
+}
+
+// Runs one logical batch as sub-batches of at most dev_batch queries; each sub-batch is optionally
+// Morton-sorted (key, index) and processed through the permutation.
+void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
+  const int64_t n = a.n;
+  const int64_t step = g->dev_batch;
+  const size_t out_row = a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL ? (size_t)a.n_vars : 1;
+  for (int64_t off = 0; off < n; off += step) {
+    const int64_t m = std::min(step, n - off);
+    QueryArgs b = a;
+    b.n = m;
+    b.r = a.r + 3 * off;
+    b.i_cell = a.i_cell ? a.i_cell + off : nullptr;
+    b.out_f64 = a.out_f64 ? a.out_f64 + out_row * off : nullptr;
+    b.out_i32 = a.out_i32 ? a.out_i32 + off : nullptr;
+    b.perm = nullptr;
+    if (want_sort(g, a.mode, m)) {
+      const int end_bit = morton_end_bit(g->dg);
+      g->keys.ensure(m); g->keys_alt.ensure(m); g->idx.ensure(m); g->idx_alt.ensure(m);
+      g->sort_temp.ensure(sort_temp_bytes(m, end_bit));
+      g->n_launches += launch_morton_sort(g->dg, m, b.r, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
+                                          g->sort_temp.p, g->sort_temp.n, nullptr, s);
+      b.perm = g->idx_alt.p;
+    }
+    g->n_launches += launch_query(g->dg, b, s);
+    CU(cudaGetLastError());
+  }
+  g->n_queries += n;
+}
+
+int check_query_args(const iu_b200_grid* g, int64_t n, const void* r, int mode, int n_vars, const int32_t* i_vars, int i_var) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  if (n < 0) { set_error("negative query count"); return IU_B200_EINVAL; }
+  if (n > 0 && !r) { set_error("null query array"); return IU_B200_EINVAL; }
+  if (mode == QM_INTERP || mode == QM_INTERP_ICELL) {
+    if (n_vars < 1 || n_vars > MAX_VARS || !i_vars) { set_error("n_vars must be in 1..32"); return IU_B200_EINVAL; }
+    for (int v = 0; v < n_vars; ++v)
+      if (i_vars[v] < 1 || i_vars[v] > g->dg.n_pd) { set_error("i_vars: column outside 1..n_point_data"); return IU_B200_EINVAL; }
+  } else if (mode == QM_CELL_F64) {
+    if (i_var < 1 || i_var > g->dg.n_cd) { set_error("i_var outside 1..n_cell_data"); return IU_B200_EINVAL; }
+  } else if (mode == QM_CELL_I32) {
+    if (i_var < 1 || i_var > g->dg.n_icd) { set_error("i_var outside 1..n_icell_data"); return IU_B200_EINVAL; }
+  }
+  return IU_B200_OK;
+}
+
+QueryArgs make_args(const iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
+                    int32_t* i_cell, double* out_f64, int32_t* out_i32) {
+  QueryArgs a;
+  a.mode = mode; a.n = n; a.r = r; a.i_cell = i_cell; a.out_f64 = out_f64; a.out_i32 = out_i32;
+  a.max_steps = (int)g->max_walk_steps;
+  if (mode == QM_INTERP || mode == QM_INTERP_ICELL) {
+    a.n_vars = n_vars;
+    for (int v = 0; v < n_vars; ++v) a.ivars[v] = i_vars[v] - 1;
+  } else if (mode == QM_CELL_F64 || mode == QM_CELL_I32) {
+    a.n_vars = 1;
+    a.ivars[0] = i_var - 1;
+  }
+  return a;
+}
+
+int query_dev(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
+              int32_t* i_cell, double* out_f64, int32_t* out_i32, void* stream) {
+  int rc = check_query_args(g, n, r, mode, n_vars, i_vars, i_var);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    run_query(g, make_args(g, mode, n, r, n_vars, i_vars, i_var, i_cell, out_f64, out_i32), (cudaStream_t)stream);
+    return IU_B200_OK;
+  });
+}
+
+int walk_args_ok(const iu_b200_grid* g, int64_t n, int max_steps, const void* r0, const void* r1, const void* ic0,
+                 const void* ic1, const void* r_p, const void* n_steps, const void* status, int mask) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  if (n < 0 || max_steps < 0) { set_error("negative count"); return IU_B200_EINVAL; }
+  if (n > 0 && (!r0 || !r1 || !ic0 || !ic1 || !r_p || !n_steps || !status)) { set_error("null array"); return IU_B200_EINVAL; }
+  if (mask < 0 || mask > g->dg.n_icd) { set_error("i_icell_mask outside 0..n_icell_data"); return IU_B200_EINVAL; }
+  return IU_B200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int iu_b200_find_nearby_cell_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int32_t* idx, void* stream) {
+  return query_dev(g, QM_NEAREST, n, r, 0, nullptr, 0, nullptr, nullptr, idx, stream);
+}
+int iu_b200_get_cell_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int32_t* i_cell, void* stream) {
+  return query_dev(g, QM_CELL, n, r, 0, nullptr, 0, i_cell, nullptr, nullptr, stream);
+}
+int iu_b200_interpolate_at_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
+                                     double* var_at_r, int32_t* i_cell, void* stream) {
+  return query_dev(g, QM_INTERP, n, r, n_vars, i_vars, 0, i_cell, var_at_r, nullptr, stream);
+}
+int iu_b200_interpolate_at_icell_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
+                                           double* var_at_r, const int32_t* i_cell, void* stream) {
+  return query_dev(g, QM_INTERP_ICELL, n, r, n_vars, i_vars, 0, const_cast<int32_t*>(i_cell), var_at_r, nullptr, stream);
+}
+int iu_b200_get_cell_scalar_at_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int i_var, int32_t* i_guess,
+                                         double* res, void* stream) {
+  return query_dev(g, QM_CELL_F64, n, r, 0, nullptr, i_var, i_guess, res, nullptr, stream);
+}
+int iu_b200_get_icell_scalar_at_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int i_var, int32_t* i_guess,
+                                          int32_t* res, void* stream) {
+  return query_dev(g, QM_CELL_I32, n, r, 0, nullptr, i_var, i_guess, nullptr, res, stream);
+}
+
+int iu_b200_get_cell_through_neighbors_batch_dev(iu_b200_grid* g, int64_t n, int max_steps, const double* r0,
+                                                 const double* r1, const int32_t* ic0, int32_t* ic1, double* r_p,
+                                                 int32_t* n_steps, int32_t* status, int i_icell_mask, void* stream) {
+  int rc = walk_args_ok(g, n, max_steps, r0, r1, ic0, ic1, r_p, n_steps, status, i_icell_mask);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    WalkArgs a;
+    a.n = n; a.max_steps = max_steps; a.r0 = r0; a.r1 = r1; a.ic0 = ic0; a.ic1 = ic1; a.r_p = r_p;
+    a.n_steps = n_steps; a.status = status; a.mask_col = i_icell_mask - 1;
+    g->n_launches += launch_walk(g->dg, a, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    g->n_queries += n;
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_check_dev(iu_b200_grid* g, void* stream) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    CU(cudaStreamSynchronize((cudaStream_t)stream));
+    unsigned long long c[CNT_N];
+    CU(cudaMemcpy(c, g->dg.counters, sizeof(c), cudaMemcpyDeviceToHost));
+    const bool bad = c[CNT_HINT_ERROR] != g->seen[CNT_HINT_ERROR];
+    g->seen[CNT_HINT_ERROR] = c[CNT_HINT_ERROR];
+    if (bad) {
+      set_error("i_cell > ug%n_cells (or a start cell outside 1..n_cells)");
+      return IU_B200_EHINT;
+    }
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_generate_queries_dev(iu_b200_grid* g, int64_t n, int64_t first, uint64_t seed, const double lo[3],
+                                 const double hi[3], double* r, void* stream) {
+  if (!g || !lo || !hi || (n > 0 && !r) || n < 0) { set_error("bad argument"); return IU_B200_EINVAL; }
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    g->n_launches += launch_generate_queries(n, first, seed, lo, hi, r, (cudaStream_t)stream);
+    CU(cudaGetLastError());
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_export_geometry(iu_b200_grid* g, double* cell_points, double* cell_face_normals, double* cell_volume,
+                            double* cell_centers) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t nc = (size_t)g->dg.n_cells, ppc = (size_t)g->dg.ppc;
+    DevBuf<double> cp, fn, vol, ce;
+    if (cell_points) cp.alloc(nc * ppc * 3);
+    if (cell_face_normals) fn.alloc(nc * ppc * 3);
+    if (cell_volume) vol.alloc(nc);
+    if (cell_centers) ce.alloc(nc * 3);
+    g->n_launches += launch_export_geometry(g->dg, cp.p, fn.p, vol.p, ce.p, nullptr);
+    CU(cudaDeviceSynchronize());
+    if (cell_points) CU(cudaMemcpy(cell_points, cp.p, cp.n * 8, cudaMemcpyDeviceToHost));
+    if (cell_face_normals) CU(cudaMemcpy(cell_face_normals, fn.p, fn.n * 8, cudaMemcpyDeviceToHost));
+    if (cell_volume) CU(cudaMemcpy(cell_volume, vol.p, vol.n * 8, cudaMemcpyDeviceToHost));
+    if (cell_centers) CU(cudaMemcpy(cell_centers, ce.p, ce.n * 8, cudaMemcpyDeviceToHost));
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_build_cell_neighbors(int cell_type, int32_t n_points, int32_t n_cells, const double* points,
+                                 const int32_t* cells, int32_t* neighbors) {
+  if (!points || !cells || !neighbors || n_points < 0 || n_cells < 0) { set_error("bad argument"); return IU_B200_EINVAL; }
+  try {
+    return build_cell_neighbors(cell_type, n_points, n_cells, points, cells, neighbors) ? IU_B200_OK : IU_B200_EINVAL;
+  } catch (const std::bad_alloc&) {
+    set_error("out of host memory");
+    return IU_B200_ENOMEM;
+  }
+}
+
+void* iu_b200_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) {
+    set_error("cudaMallocHost failed");
+    return nullptr;
+  }
+  return p;
+}
+void iu_b200_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// the hot path on host buffers: three-slot pipeline  H2D (s_in) | kernels (s_comp) | D2H (s_out)
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+void* stage_buffer(iu_b200_grid* g, size_t bytes) {
+  if (bytes > g->h_stage_bytes) {
+    if (g->h_stage) cudaFreeHost(g->h_stage);
+    g->h_stage = nullptr;
+    g->h_stage_bytes = 0;
+    CU(cudaMallocHost(&g->h_stage, bytes));
+    g->h_stage_bytes = bytes;
+  }
+  return g->h_stage;
+}
+
+// H2D(slot, off, m) enqueues on s_in; COMPUTE(slot, m) on s_comp; D2H(slot, off, m, merge) on s_out.
+// `merge` is true when the chunk's `trigger` counter moved, i.e. some output rows must stay
+// untouched in the caller's arrays; D2H then goes through pinned staging and a host-side row copy.
+template <class H2D, class COMPUTE, class D2H>
+int run_pipeline(iu_b200_grid* g, int64_t n, int trigger, H2D&& h2d, COMPUTE&& compute, D2H&& d2h) {
+  CU(cudaDeviceSynchronize());
+  unsigned long long last[CNT_N], base[CNT_N];
+  CU(cudaMemcpy(base, g->dg.counters, sizeof(base), cudaMemcpyDeviceToHost));
+  std::memcpy(last, base, sizeof(last));
+  const int64_t chunk = g->host_chunk;
+  const int64_t n_chunks = (n + chunk - 1) / chunk;
+  for (int64_t c = 0; c <= n_chunks; ++c) {
+    if (c < n_chunks) {
+      Slot& sl = g->slot[c % N_SLOTS];
+      const int64_t off = c * chunk, m = std::min(chunk, n - off);
+      if (c >= N_SLOTS) CU(cudaStreamWaitEvent(g->s_in, sl.out_done, 0));
+      h2d(sl, off, m);
+      CU(cudaEventRecord(sl.in_done, g->s_in));
+      CU(cudaStreamWaitEvent(g->s_comp, sl.in_done, 0));
+      compute(sl, m);
+      CU(cudaMemcpyAsync(g->h_counters + (c % N_SLOTS) * CNT_N, g->dg.counters, CNT_N * sizeof(unsigned long long),
+                         cudaMemcpyDeviceToHost, g->s_comp));
+      CU(cudaEventRecord(sl.comp_done, g->s_comp));
+    }
+    const int64_t d = c - 1;
+    if (d >= 0) {
+      Slot& sl = g->slot[d % N_SLOTS];
+      const int64_t off = d * chunk, m = std::min(chunk, n - off);
+      CU(cudaEventSynchronize(sl.comp_done));
+      const unsigned long long* now = g->h_counters + (d % N_SLOTS) * CNT_N;
+      const bool merge = now[trigger] != last[trigger];
+      std::memcpy(last, now, sizeof(last));
+      CU(cudaStreamWaitEvent(g->s_out, sl.comp_done, 0));
+      d2h(sl, off, m, merge);
+      CU(cudaEventRecord(sl.out_done, g->s_out));
+    }
+  }
+  CU(cudaStreamSynchronize(g->s_out));
+  const bool bad = last[CNT_HINT_ERROR] != base[CNT_HINT_ERROR];
+  g->seen[CNT_HINT_ERROR] = last[CNT_HINT_ERROR];
+  if (bad) {
+    set_error("i_cell > ug%n_cells (or a start cell outside 1..n_cells)");
+    return IU_B200_EHINT;
+  }
+  return IU_B200_OK;
+}
+
+int query_host(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
+               int32_t* i_cell, double* out_f64, int32_t* out_i32) {
+  int rc = check_query_args(g, n, r, mode, n_vars, i_vars, i_var);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  if (mode != QM_NEAREST && !i_cell) { set_error("null i_cell array"); return IU_B200_EINVAL; }
+  const bool f64_out = mode == QM_INTERP || mode == QM_INTERP_ICELL || mode == QM_CELL_F64;
+  const bool i32_out = mode == QM_NEAREST || mode == QM_CELL_I32;
+  if ((f64_out && !out_f64) || (i32_out && !out_i32)) { set_error("null output array"); return IU_B200_EINVAL; }
+  const size_t row = mode == QM_INTERP || mode == QM_INTERP_ICELL ? (size_t)n_vars : 1;   // output words per query
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t cap = (size_t)std::min<int64_t>(g->host_chunk, n);
+    for (Slot& sl : g->slot) {
+      sl.r.ensure(3 * cap);
+      if (mode != QM_NEAREST) sl.i_a.ensure(cap);
+      if (f64_out) sl.out_f64.ensure(row * cap);
+      if (i32_out) sl.i_b.ensure(cap);
+    }
+    auto h2d = [&](Slot& sl, int64_t off, int64_t m) {
+      CU(cudaMemcpyAsync(sl.r.p, r + 3 * off, (size_t)m * 24, cudaMemcpyHostToDevice, g->s_in));
+      if (mode != QM_NEAREST) CU(cudaMemcpyAsync(sl.i_a.p, i_cell + off, (size_t)m * 4, cudaMemcpyHostToDevice, g->s_in));
+    };
+    auto compute = [&](Slot& sl, int64_t m) {
+      run_query(g, make_args(g, mode, m, sl.r.p, n_vars, i_vars, i_var, sl.i_a.p, sl.out_f64.p, sl.i_b.p), g->s_comp);
+    };
+    auto d2h = [&](Slot& sl, int64_t off, int64_t m, bool merge) {
+      if (mode != QM_NEAREST && mode != QM_INTERP_ICELL)
+        CU(cudaMemcpyAsync(i_cell + off, sl.i_a.p, (size_t)m * 4, cudaMemcpyDeviceToHost, g->s_out));
+      if (mode == QM_CELL) return;
+      const size_t row_bytes = f64_out ? row * 8 : 4;
+      char* dst = f64_out ? (char*)(out_f64 + row * off) : (char*)(out_i32 + off);
+      const void* src = f64_out ? (const void*)sl.out_f64.p : (const void*)sl.i_b.p;
+      if (!merge || mode == QM_NEAREST) {
+        CU(cudaMemcpyAsync(dst, src, (size_t)m * row_bytes, cudaMemcpyDeviceToHost, g->s_out));
+        return;
+      }
+      // some queries of this chunk were not found: their rows stay untouched (:447, :461, :492)
+      char* st = (char*)stage_buffer(g, (size_t)g->host_chunk * row_bytes);
+      CU(cudaMemcpyAsync(st, src, (size_t)m * row_bytes, cudaMemcpyDeviceToHost, g->s_out));
+      CU(cudaStreamSynchronize(g->s_out));
+      const int32_t* ic = i_cell + off;
+      for (int64_t i = 0; i < m; ++i)
+        if (ic[i] >= 1) std::memcpy(dst + (size_t)i * row_bytes, st + (size_t)i * row_bytes, row_bytes);
+    };
+    return run_pipeline(g, n, CNT_NOT_FOUND, h2d, compute, d2h);
+  });
+}
+
+}  // namespace
+
+extern "C" {
+
+int iu_b200_find_nearby_cell_batch(iu_b200_grid* g, int64_t n, const double* r, int32_t* idx) {
+  return query_host(g, QM_NEAREST, n, r, 0, nullptr, 0, nullptr, nullptr, idx);
+}
+int iu_b200_get_cell_batch(iu_b200_grid* g, int64_t n, const double* r, int32_t* i_cell) {
+  return query_host(g, QM_CELL, n, r, 0, nullptr, 0, i_cell, nullptr, nullptr);
+}
+int iu_b200_interpolate_at_batch(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
+                                 double* var_at_r, int32_t* i_cell) {
+  return query_host(g, QM_INTERP, n, r, n_vars, i_vars, 0, i_cell, var_at_r, nullptr);
+}
+int iu_b200_interpolate_scalar_at_batch(iu_b200_grid* g, int64_t n, const double* r, int i_var, double* var_at_r,
+                                        int32_t* i_cell) {
+  const int32_t iv[1] = {i_var};
+  return query_host(g, QM_INTERP, n, r, 1, iv, 0, i_cell, var_at_r, nullptr);
+}
+int iu_b200_interpolate_at_icell_batch(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
+                                       double* var_at_r, const int32_t* i_cell) {
+  return query_host(g, QM_INTERP_ICELL, n, r, n_vars, i_vars, 0, const_cast<int32_t*>(i_cell), var_at_r, nullptr);
+}
+int iu_b200_get_cell_scalar_at_batch(iu_b200_grid* g, int64_t n, const double* r, int i_var, int32_t* i_guess, double* res) {
+  return query_host(g, QM_CELL_F64, n, r, 0, nullptr, i_var, i_guess, res, nullptr);
+}
+int iu_b200_get_icell_scalar_at_batch(iu_b200_grid* g, int64_t n, const double* r, int i_var, int32_t* i_guess, int32_t* res) {
+  return query_host(g, QM_CELL_I32, n, r, 0, nullptr, i_var, i_guess, nullptr, res);
+}
+
+int iu_b200_get_cell_through_neighbors_batch(iu_b200_grid* g, int64_t n, int max_steps, const double* r0, const double* r1,
+                                             const int32_t* ic0, int32_t* ic1, double* r_p, int32_t* n_steps,
+                                             int32_t* status, int i_icell_mask) {
+  int rc = walk_args_ok(g, n, max_steps, r0, r1, ic0, ic1, r_p, n_steps, status, i_icell_mask);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t cap = (size_t)std::min<int64_t>(g->host_chunk, n);
+    for (Slot& sl : g->slot) {
+      sl.r.ensure(3 * cap); sl.r1.ensure(3 * cap); sl.out_f64.ensure(3 * cap);
+      sl.i_a.ensure(cap); sl.i_b.ensure(cap); sl.i_c.ensure(cap); sl.i_d.ensure(cap);
+    }
+    auto h2d = [&](Slot& sl, int64_t off, int64_t m) {
+      CU(cudaMemcpyAsync(sl.r.p, r0 + 3 * off, (size_t)m * 24, cudaMemcpyHostToDevice, g->s_in));
+      CU(cudaMemcpyAsync(sl.r1.p, r1 + 3 * off, (size_t)m * 24, cudaMemcpyHostToDevice, g->s_in));
+      CU(cudaMemcpyAsync(sl.i_a.p, ic0 + off, (size_t)m * 4, cudaMemcpyHostToDevice, g->s_in));
+    };
+    auto compute = [&](Slot& sl, int64_t m) {
+      WalkArgs a;
+      a.n = m; a.max_steps = max_steps; a.r0 = sl.r.p; a.r1 = sl.r1.p; a.ic0 = sl.i_a.p; a.ic1 = sl.i_b.p;
+      a.r_p = sl.out_f64.p; a.n_steps = sl.i_c.p; a.status = sl.i_d.p; a.mask_col = i_icell_mask - 1;
+      a.mark_early = true;
+      g->n_launches += launch_walk(g->dg, a, g->s_comp);
+      CU(cudaGetLastError());
+      g->n_queries += m;
+    };
+    auto d2h = [&](Slot& sl, int64_t off, int64_t m, bool merge) {
+      CU(cudaMemcpyAsync(ic1 + off, sl.i_b.p, (size_t)m * 4, cudaMemcpyDeviceToHost, g->s_out));
+      CU(cudaMemcpyAsync(status + off, sl.i_d.p, (size_t)m * 4, cudaMemcpyDeviceToHost, g->s_out));
+      if (!merge) {
+        CU(cudaMemcpyAsync(r_p + 3 * off, sl.out_f64.p, (size_t)m * 24, cudaMemcpyDeviceToHost, g->s_out));
+        CU(cudaMemcpyAsync(n_steps + off, sl.i_c.p, (size_t)m * 4, cudaMemcpyDeviceToHost, g->s_out));
+        return;
+      }
+      // rays shorter than tiny_distance leave r_p and n_steps untouched (:689-692)
+      char* st = (char*)stage_buffer(g, (size_t)g->host_chunk * 28);
+      double* st_rp = (double*)st;
+      int32_t* st_ns = (int32_t*)(st + (size_t)g->host_chunk * 24);
+      CU(cudaMemcpyAsync(st_rp, sl.out_f64.p, (size_t)m * 24, cudaMemcpyDeviceToHost, g->s_out));
+      CU(cudaMemcpyAsync(st_ns, sl.i_c.p, (size_t)m * 4, cudaMemcpyDeviceToHost, g->s_out));
+      CU(cudaStreamSynchronize(g->s_out));
+      for (int64_t i = 0; i < m; ++i)
+        if (st_ns[i] != INT32_MIN) {
+          n_steps[off + i] = st_ns[i];
+          for (int k = 0; k < 3; ++k) r_p[3 * (off + i) + k] = st_rp[3 * i + k];
+        }
+    };
+    return run_pipeline(g, n, CNT_EARLY, h2d, compute, d2h);
+  });
+}
+
+}  // extern "C"

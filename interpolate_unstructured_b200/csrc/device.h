@@ -33,7 +33,7 @@ enum QueryMode : int {
 };
 
 // counters (device, unsigned long long each)
-enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_N = 4 };
+enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_EARLY = 3, CNT_N = 4 };
 
 struct DeviceGrid {
   int cell_type = 0, ppc = 0, n_cells = 0, n_points = 0;
@@ -81,6 +81,7 @@ struct WalkArgs {
   int32_t* n_steps = nullptr;
   int32_t* status = nullptr;
   int mask_col = -1;                // 0-based icell_data column, -1 = absent
+  bool mark_early = false;          // write n_steps = INT32_MIN for rays shorter than tiny_distance (host pipeline)
 };
 
 // every launcher returns the number of kernels it launched (for IU_B200_STAT_KERNEL_LAUNCHES)

@@ -9,6 +9,12 @@ namespace iu {
 constexpr int LEAF = 8;           // centres per kd-tree leaf block (fixed trip count on the device)
 constexpr int MAX_VARS = 32;      // variables per launch of the interpolation kernel
 
+// cell types (m_interp_unstructured.f90:13-15) and the per-query "step cap hit" sentinel
+constexpr int IU_TRIANGLE_CT = 1;
+constexpr int IU_QUAD_CT = 2;
+constexpr int IU_TETRA_CT = 3;
+constexpr int IU_WALK_LIMIT = -2;
+
 void set_error(const std::string& msg);
 
 // ---- BINDA container (m_binda.f90:52-194; written by convert_to_binary.py:68-115) ----------

@@ -498,7 +498,7 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_query(const QueryKernelParams
     } else if (MODE == QM_INTERP_ICELL) {
       const int h = P.i_cell[i];
       if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }
-      if (h < 1) continue;
+      if (h < 1) { atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
       ic = __ldg(P.dev_of_orig + h);
     } else {
       const int h = P.i_cell[i];
@@ -538,7 +538,7 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_query(const QueryKernelParams
       W.setup(p, __ldg(R + L::VOL), V3{qx, qy, qz});
       double* out = P.out_f64 + (size_t)i * P.n_vars;
       if (NV > 0) {
-        double res[NV];
+        double res[NV > 0 ? NV : 1];
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
           double d[4];
@@ -580,6 +580,9 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_walk(const double* __restrict
     if (!early) {   // r_p / n_steps undefined on the early return, :689-692
       a.r_p[3 * i] = r_p.x; a.r_p[3 * i + 1] = r_p.y; a.r_p[3 * i + 2] = r_p.z;
       a.n_steps[i] = n_steps;
+    } else {
+      atomicAdd(counters + CNT_EARLY, 1ULL);
+      if (a.mark_early) a.n_steps[i] = INT32_MIN;
     }
   }
 }
