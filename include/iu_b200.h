@@ -53,6 +53,7 @@ extern "C" {
 #define IU_B200_OPT_MAX_WALK_STEPS 2 /* step cap used where the reference passes huge(1); default 2^20 */
 #define IU_B200_OPT_HOST_CHUNK 3    /* queries per H2D/compute/D2H pipeline chunk (host API)      */
 #define IU_B200_OPT_DEV_BATCH 4     /* max queries per internal device sub-batch (workspace bound) */
+#define IU_B200_OPT_TIME_KERNELS 5  /* 1: bracket the hot kernel and the sort with CUDA events (stats 7..9) */
 
 /* indices into the int64 array filled by iu_b200_get_stats */
 #define IU_B200_STAT_KERNEL_LAUNCHES 0 /* kernels of this library launched since creation/reset */
@@ -62,7 +63,10 @@ extern "C" {
 #define IU_B200_STAT_MESH_BYTES 4
 #define IU_B200_STAT_TREE_DEPTH 5
 #define IU_B200_STAT_NOT_FOUND 6       /* queries that ended with i_cell <= 0 */
-#define IU_B200_N_STATS 8
+#define IU_B200_STAT_QUERY_KERNEL_NS 7  /* with IU_B200_OPT_TIME_KERNELS: summed device time of the hot kernel */
+#define IU_B200_STAT_QUERY_KERNEL_LAUNCHES 8
+#define IU_B200_STAT_SORT_NS 9         /* same for Morton keys + radix sort */
+#define IU_B200_N_STATS 12
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */
 

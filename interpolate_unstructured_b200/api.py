@@ -28,9 +28,9 @@ TRIANGLE, QUAD, TETRA = 1, 2, 3
 CELL_TYPES = {"triangle": TRIANGLE, "quad": QUAD, "tetra": TETRA}
 E_INVAL, E_CUDA, E_IO, E_HINT, E_NOMEM = -1, -2, -3, -4, -5
 CELL_WALK_LIMIT = -2
-OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH = 1, 2, 3, 4
+OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KERNELS = 1, 2, 3, 4, 5
 STAT_NAMES = ["kernel_launches", "walk_limit_hits", "queries", "workspace_bytes", "mesh_bytes", "tree_depth",
-              "not_found", "reserved"]
+              "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "reserved10", "reserved11"]
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)
@@ -328,7 +328,7 @@ class Grid:
         _check(lib().iu_b200_set_option(self._h, int(option), int(value)))
 
     def stats(self):
-        s = (C.c_int64 * 8)()
+        s = (C.c_int64 * 12)()
         _check(lib().iu_b200_get_stats(self._h, s))
         return dict(zip(STAT_NAMES, (int(x) for x in s)))
 

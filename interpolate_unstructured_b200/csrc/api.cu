@@ -100,6 +100,13 @@ struct iu_b200_grid {
   void* h_stage = nullptr;                     // pinned staging for the rare "merge" path
   size_t h_stage_bytes = 0;
   unsigned long long seen[CNT_N] = {0, 0, 0, 0};   // counter values already accounted for
+  // optional per-kernel timing (IU_B200_OPT_TIME_KERNELS): event pairs around the hot kernel and the sort
+  bool time_kernels = false;
+  struct Timed { cudaEvent_t a, b; int kind; };
+  std::vector<Timed> pending;
+  std::vector<cudaEvent_t> event_pool;
+  double timed_ns[2] = {0, 0};
+  int64_t timed_launches[2] = {0, 0};
   std::mutex mu;   // one batch call at a time per grid (workspaces are per grid)
 };
 
@@ -122,6 +129,41 @@ size_t workspace_bytes(const iu_b200_grid* g) {
   for (const Slot& s : g->slot)
     b += (s.r.n + s.r1.n + s.out_f64.n) * 8 + (s.i_a.n + s.i_b.n + s.i_c.n + s.i_d.n) * 4;
   return b;
+}
+
+cudaEvent_t timing_event(iu_b200_grid* g) {
+  cudaEvent_t e = nullptr;
+  if (!g->event_pool.empty()) { e = g->event_pool.back(); g->event_pool.pop_back(); }
+  else CU(cudaEventCreate(&e));
+  return e;
+}
+
+// kind 0 = hot query kernel, 1 = Morton keys + radix sort
+struct TimedScope {
+  iu_b200_grid* g; cudaStream_t s; int kind; cudaEvent_t a = nullptr;
+  TimedScope(iu_b200_grid* g_, cudaStream_t s_, int kind_) : g(g_), s(s_), kind(kind_) {
+    if (g->time_kernels) { a = timing_event(g); CU(cudaEventRecord(a, s)); }
+  }
+  void stop() {
+    if (!a) return;
+    cudaEvent_t b = timing_event(g);
+    CU(cudaEventRecord(b, s));
+    g->pending.push_back({a, b, kind});
+    a = nullptr;
+  }
+};
+
+void collect_timings(iu_b200_grid* g) {
+  for (auto& t : g->pending) {
+    float ms = 0;
+    if (cudaEventSynchronize(t.b) == cudaSuccess && cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) {
+      g->timed_ns[t.kind] += (double)ms * 1e6;
+      g->timed_launches[t.kind] += 1;
+    }
+    g->event_pool.push_back(t.a);
+    g->event_pool.push_back(t.b);
+  }
+  g->pending.clear();
 }
 
 void free_device_grid(DeviceGrid& d) {
@@ -337,6 +379,8 @@ int iu_b200_grid_destroy(iu_b200_grid* g) {
     if (g->s_out) cudaStreamDestroy(g->s_out);
     if (g->h_counters) cudaFreeHost(g->h_counters);
     if (g->h_stage) cudaFreeHost(g->h_stage);
+    collect_timings(g);
+    for (cudaEvent_t e : g->event_pool) cudaEventDestroy(e);
   }
   delete g;
   return IU_B200_OK;
@@ -513,6 +557,10 @@ int iu_b200_set_option(iu_b200_grid* g, int option, int64_t value) {
       if (value < 1 || value > (1LL << 31)) break;
       g->dev_batch = value;
       return IU_B200_OK;
+    case IU_B200_OPT_TIME_KERNELS:
+      if (value < 0 || value > 1) break;
+      g->time_kernels = value != 0;
+      return IU_B200_OK;
     default:
       set_error("unknown option");
       return IU_B200_EINVAL;
@@ -535,6 +583,10 @@ int iu_b200_get_stats(const iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
     stats[IU_B200_STAT_MESH_BYTES] = (int64_t)g->mesh_bytes;
     stats[IU_B200_STAT_TREE_DEPTH] = g->tree_depth;
     stats[IU_B200_STAT_NOT_FOUND] = (int64_t)c[CNT_NOT_FOUND];
+    collect_timings(const_cast<iu_b200_grid*>(g));
+    stats[IU_B200_STAT_QUERY_KERNEL_NS] = (int64_t)g->timed_ns[0];
+    stats[IU_B200_STAT_QUERY_KERNEL_LAUNCHES] = g->timed_launches[0];
+    stats[IU_B200_STAT_SORT_NS] = (int64_t)g->timed_ns[1];
     return IU_B200_OK;
   });
 }
@@ -554,6 +606,9 @@ int iu_b200_reset_stats(iu_b200_grid* g) {
     for (int i = 0; i < CNT_N; ++i) g->seen[i] = c[i];
     g->n_launches = 0;
     g->n_queries = 0;
+    collect_timings(g);
+    g->timed_ns[0] = g->timed_ns[1] = 0;
+    g->timed_launches[0] = g->timed_launches[1] = 0;
     return IU_B200_OK;
   });
 }
@@ -591,11 +646,15 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
       const int end_bit = morton_end_bit(g->dg);
       g->keys.ensure(m); g->keys_alt.ensure(m); g->idx.ensure(m); g->idx_alt.ensure(m);
       g->sort_temp.ensure(sort_temp_bytes(m, end_bit));
+      TimedScope ts(g, s, 1);
       g->n_launches += launch_morton_sort(g->dg, m, b.r, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
                                           g->sort_temp.p, g->sort_temp.n, nullptr, s);
+      ts.stop();
       b.perm = g->idx_alt.p;
     }
+    TimedScope tq(g, s, 0);
     g->n_launches += launch_query(g->dg, b, s);
+    tq.stop();
     CU(cudaGetLastError());
   }
   g->n_queries += n;
