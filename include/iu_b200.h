@@ -132,6 +132,13 @@ int iu_b200_update_point_data(iu_b200_grid* grid, int col0, int n_cols, const do
 int iu_b200_update_cell_data(iu_b200_grid* grid, int col0, int n_cols, const double* data);
 int iu_b200_update_icell_data(iu_b200_grid* grid, int col0, int n_cols, const int32_t* data);
 
+/* The reverse direction: read device columns col0 .. col0+n_cols-1 back into a column-major host
+ * array (n_points|n_cells, n_cols).  The Fortran shim fills its ug%point_data / ug%cell_data /
+ * ug%icell_data mirrors with these after iu_read_grid (:875-911). */
+int iu_b200_download_point_data(iu_b200_grid* grid, int col0, int n_cols, double* data);
+int iu_b200_download_cell_data(iu_b200_grid* grid, int col0, int n_cols, double* data);
+int iu_b200_download_icell_data(iu_b200_grid* grid, int col0, int n_cols, int32_t* data);
+
 int iu_b200_set_option(iu_b200_grid* grid, int option, int64_t value);
 int iu_b200_get_stats(const iu_b200_grid* grid, int64_t stats[IU_B200_N_STATS]);
 int iu_b200_reset_stats(iu_b200_grid* grid);

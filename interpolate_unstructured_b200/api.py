@@ -73,6 +73,9 @@ _SIGNATURES = {
     "iu_b200_update_point_data": (C.c_int, [c_vp, C.c_int, C.c_int, c_dp]),
     "iu_b200_update_cell_data": (C.c_int, [c_vp, C.c_int, C.c_int, c_dp]),
     "iu_b200_update_icell_data": (C.c_int, [c_vp, C.c_int, C.c_int, c_ip]),
+    "iu_b200_download_point_data": (C.c_int, [c_vp, C.c_int, C.c_int, c_dp]),
+    "iu_b200_download_cell_data": (C.c_int, [c_vp, C.c_int, C.c_int, c_dp]),
+    "iu_b200_download_icell_data": (C.c_int, [c_vp, C.c_int, C.c_int, c_ip]),
     "iu_b200_set_option": (C.c_int, [c_vp, C.c_int, C.c_int64]),
     "iu_b200_get_stats": (C.c_int, [c_vp, C.POINTER(C.c_int64)]),
     "iu_b200_reset_stats": (C.c_int, [c_vp]),
@@ -323,6 +326,22 @@ class Grid:
         v = v[:, None] if v.ndim == 1 else v
         t = np.ascontiguousarray(v.T)
         _check(lib().iu_b200_update_icell_data(self._h, int(i_var), t.shape[0], t.ctypes.data_as(c_ip)))
+
+    def get_point_data(self, i_var, n_cols=1):
+        """``ug%point_data(:, i_var:i_var+n_cols-1)`` read back from the device, shape (n_points, n_cols)."""
+        t = np.empty((int(n_cols), self.n_points))
+        _check(lib().iu_b200_download_point_data(self._h, int(i_var), int(n_cols), t.ctypes.data_as(c_dp)))
+        return np.ascontiguousarray(t.T)
+
+    def get_cell_data(self, i_var, n_cols=1):
+        t = np.empty((int(n_cols), self.n_cells))
+        _check(lib().iu_b200_download_cell_data(self._h, int(i_var), int(n_cols), t.ctypes.data_as(c_dp)))
+        return np.ascontiguousarray(t.T)
+
+    def get_icell_data(self, i_var, n_cols=1):
+        t = np.empty((int(n_cols), self.n_cells), dtype=np.int32)
+        _check(lib().iu_b200_download_icell_data(self._h, int(i_var), int(n_cols), t.ctypes.data_as(c_ip)))
+        return np.ascontiguousarray(t.T)
 
     def set_option(self, option, value):
         _check(lib().iu_b200_set_option(self._h, int(option), int(value)))

@@ -538,6 +538,47 @@ int iu_b200_update_icell_data(iu_b200_grid* g, int col0, int n_cols, const int32
   });
 }
 
+int iu_b200_download_point_data(iu_b200_grid* g, int col0, int n_cols, double* data) {
+  if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
+  if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_pd) { set_error("point_data column range outside 1..n_point_data"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    DevBuf<double> cols;
+    cols.alloc((size_t)g->dg.n_points * n_cols);
+    CU(cudaDeviceSynchronize());
+    g->n_launches += launch_unpack_point_data(g->dg, cols.p, col0 - 1, n_cols, nullptr);
+    CU(cudaMemcpy(data, cols.p, cols.n * 8, cudaMemcpyDeviceToHost));
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_download_cell_data(iu_b200_grid* g, int col0, int n_cols, double* data) {
+  if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
+  if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_cd) { set_error("cell_data column range outside 1..n_cell_data"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t nc = (size_t)g->dg.n_cells;
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(data, g->dg.cd + nc * (col0 - 1), nc * n_cols * 8, cudaMemcpyDeviceToHost));
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_download_icell_data(iu_b200_grid* g, int col0, int n_cols, int32_t* data) {
+  if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
+  if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_icd) { set_error("icell_data column range outside 1..n_icell_data"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t nc = (size_t)g->dg.n_cells;
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy(data, g->dg.icd + nc * (col0 - 1), nc * n_cols * 4, cudaMemcpyDeviceToHost));
+    return IU_B200_OK;
+  });
+}
+
 int iu_b200_set_option(iu_b200_grid* g, int option, int64_t value) {
   if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
   switch (option) {

@@ -195,6 +195,16 @@ __global__ void k_pack_point_data(int n_points, int n_cols, int col0, int stride
   pd[p * stride + col0 + v] = cols[i];
 }
 
+// the reverse of k_pack_point_data
+__global__ void k_unpack_point_data(int n_points, int n_cols, int col0, int stride, const double* __restrict__ pd,
+                                    double* __restrict__ cols) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_points * n_cols) return;
+  const int v = (int)(i / n_points);
+  const size_t p = i % n_points;
+  cols[i] = pd[p * stride + col0 + v];
+}
+
 __global__ void k_repack_point_data(int n_points, int n_cols, int old_stride, int new_stride, const double* __restrict__ a,
                                     double* __restrict__ b) {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -683,6 +693,13 @@ int launch_pack_point_data(const DeviceGrid& g, const double* cols, int col0, in
   const int64_t n = (int64_t)g.n_points * n_cols;
   if (n == 0) return 0;
   k_pack_point_data<<<blocks_for(n, 256), 256, 0, s>>>(g.n_points, n_cols, col0, g.pd_stride, cols, g.pd);
+  return 1;
+}
+
+int launch_unpack_point_data(const DeviceGrid& g, double* cols, int col0, int n_cols, cudaStream_t s) {
+  const int64_t n = (int64_t)g.n_points * n_cols;
+  if (n == 0) return 0;
+  k_unpack_point_data<<<blocks_for(n, 256), 256, 0, s>>>(g.n_points, n_cols, col0, g.pd_stride, g.pd, cols);
   return 1;
 }
 
