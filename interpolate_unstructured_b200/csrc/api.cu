@@ -263,6 +263,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     d.n_internal = tree.n_leaves - 1;
     d.n_sm_nodes = std::min(d.n_internal, 2047);
     for (int l = 1; l < tree.n_leaves; l <<= 1) ++g->tree_depth;
+    d.depth = g->tree_depth;
     const size_t n_slots = (size_t)tree.n_leaves * LEAF;
     CU(cudaMalloc((void**)&d.split, std::max<size_t>(1, d.n_internal) * 8));
     CU(cudaMalloc((void**)&d.sdim, std::max<size_t>(1, d.n_internal)));

@@ -39,6 +39,7 @@ struct DeviceGrid {
   int cell_type = 0, ppc = 0, n_cells = 0, n_points = 0;
   // kd-tree
   int n_leaves = 0, n_internal = 0, n_sm_nodes = 0;
+  int depth = 0;                   // levels of internal nodes = level of the deepest leaf
   double* split = nullptr;
   uint8_t* sdim = nullptr;
   double* centers4 = nullptr;      // n_leaves*LEAF x {x, y, z, bits(original id)}; padding = +inf

@@ -296,64 +296,102 @@ struct TreeView {
 };
 
 // Exact nearest centre (squared distance summed x, y, z without FMA, like kdtree2's leaf loop);
-// ties -> lowest original cell index.  Stackless traversal of the complete heap-indexed tree:
-// descend to the leaf on the query's side, scan its LEAF slots, then climb; at every ancestor
-// reached from its near child the far child is entered iff (q[dim]-split)^2 <= best.  By
-// monotonicity of fp64 subtraction, multiplication and addition, (q[dim]-split)^2 is a lower
-// bound of the COMPUTED squared distance of every centre behind the plane, so pruning with '>'
-// never drops the true fp64 minimum or a tie.  Returns the 0-based device slot, -1 if none.
-__device__ __forceinline__ int nearest_center(const TreeView& t, const double* s_split, const uint8_t* s_dim, double qx,
-                                              double qy, double qz) {
-  double best = __longlong_as_double(0x7ff0000000000000LL);
-  int besti = -1;
-  long long besto = 0x7fffffffffffffffLL;
-  int node = 0;
-  for (;;) {
-    while (node < t.n_internal) {   // descend
-      double s; int k;
-      if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
-      else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
-      const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
-      node = 2 * node + 1 + (qk < s ? 0 : 1);
-    }
-    {   // leaf scan, two batches of four slots (8 independent 16-B loads in flight each)
-      const int base = (node - t.n_internal) * LEAF;
-      const double2* c = reinterpret_cast<const double2*>(t.centers4) + 2 * (size_t)base;
+// ties -> lowest original cell index.  Depth-first traversal of the complete heap-indexed tree
+// without a node stack:
+//   * every descent step at level l stores a float LOWER bound (round-down) of the plane distance
+//     (q[dim]-split)^2 in s_lb[l][thread] and marks level l in the `pending` bit trail iff the far
+//     child may still hold a centre at distance <= best;
+//   * after a leaf scan the deepest pending level whose bound still passes is popped, the walk
+//     jumps straight to the far child there (sibling of the path node, from the heap index of the
+//     current leaf by shifts) and descends again.  Pending bits always lie on the current
+//     root-to-leaf path, so no per-level node ids are kept;
+//   * the first descent and leaf scan run with the whole warp converged (uniform tree depth); the
+//     first pop is preceded by a convergent filter of all levels against the first `best`.
+// By monotonicity of fp64 subtraction, multiplication and addition, (q[dim]-split)^2 is a lower
+// bound of the COMPUTED squared distance of every centre behind the plane, and the float bound is
+// <= it, so pruning with '>' never drops the true fp64 minimum or a tie.  Returns the 0-based
+// device slot, -1 if none.
+struct NNState {
+  double best;
+  long long besto;
+  int besti;
+};
+
+__device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx, double qy, double qz, NNState& st) {
+  // two batches of four slots (8 independent 16-B loads in flight each)
+  const int base = (node - t.n_internal) * LEAF;
+  const double2* c = reinterpret_cast<const double2*>(t.centers4) + 2 * (size_t)base;
 #pragma unroll
-      for (int h = 0; h < LEAF; h += 4) {
-        double2 a[4], b[4];
+  for (int h = 0; h < LEAF; h += 4) {
+    double2 a[4], b[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { a[j] = __ldg(c + 2 * (h + j)); b[j] = __ldg(c + 2 * (h + j) + 1); }
+    for (int j = 0; j < 4; ++j) { a[j] = __ldg(c + 2 * (h + j)); b[j] = __ldg(c + 2 * (h + j) + 1); }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const double dx = a[j].x - qx, dy = a[j].y - qy, dz = b[j].x - qz;
-          const double sd = (dx * dx + dy * dy) + dz * dz;
-          if (sd < best) { best = sd; besti = base + h + j; besto = __double_as_longlong(b[j].y); }
-          else if (sd == best && __double_as_longlong(b[j].y) < besto && __double_as_longlong(b[j].y) > 0) {
-            besti = base + h + j; besto = __double_as_longlong(b[j].y);
-          }
-        }
-      }
+    for (int j = 0; j < 4; ++j) {
+      const double dx = a[j].x - qx, dy = a[j].y - qy, dz = b[j].x - qz;
+      const double sd = (dx * dx + dy * dy) + dz * dz;
+      const long long o = __double_as_longlong(b[j].y);
+      // padding slots hold +inf centres (sd = inf or NaN): never selected because besti < 0 only
+      // while best = +inf and 'sd < best' is false for them
+      if (sd < st.best || (sd == st.best && o < st.besto && o > 0)) { st.best = sd; st.besti = base + h + j; st.besto = o; }
     }
-    bool done = false;
-    for (;;) {   // climb
-      if (node == 0) { done = true; break; }
-      const int child = node;
-      node = (node - 1) >> 1;
-      double s; int k;
-      if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
-      else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
-      const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
-      const int near_right = qk < s ? 0 : 1;
-      const int was_right = (child & 1) ? 0 : 1;
-      if (was_right == near_right) {
-        const double d = qk - s;
-        if (!(d * d > best)) { node = 2 * node + 1 + (1 - near_right); break; }
-      }
-    }
-    if (done) break;
   }
-  return besti;
+}
+
+__device__ __forceinline__ int nearest_center(const TreeView& t, const double* s_split, const uint8_t* s_dim, float* s_lb,
+                                              double qx, double qy, double qz) {
+  NNState st{__longlong_as_double(0x7ff0000000000000LL), 0x7fffffffffffffffLL, -1};
+  float* lb = s_lb + threadIdx.x;   // lb[l * QUERY_THREADS]
+  uint32_t pending = 0;
+  int node = 0, lvl = 0;
+  // first descent: best = +inf, every level stays pending until the filter below
+  while (node < t.n_internal) {
+    double s; int k;
+    if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
+    else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
+    const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
+    const double d = qk - s;
+    lb[lvl * QUERY_THREADS] = __double2float_rd(d * d);
+    node = 2 * node + 1 + (qk < s ? 0 : 1);
+    ++lvl;
+  }
+  scan_leaf(t, node, qx, qy, qz, st);
+  {
+    const float bf = __double2float_ru(st.best);
+    for (int l = 0; l < lvl; ++l)
+      if (!(lb[l * QUERY_THREADS] > bf)) pending |= 1u << l;
+  }
+  for (;;) {
+    // pop the deepest pending level that still passes
+    const float bf = __double2float_ru(st.best);
+    bool found = false;
+    while (pending) {
+      const int l = 31 - __clz(pending);
+      pending ^= 1u << l;
+      if (!(lb[l * QUERY_THREADS] > bf)) {
+        const int p1 = (node + 1) >> (lvl - (l + 1));   // 1-based heap index of the path node at level l+1
+        node = (p1 ^ 1) - 1;                            // its sibling = the far child at level l
+        lvl = l + 1;
+        found = true;
+        break;
+      }
+    }
+    if (!found) break;
+    while (node < t.n_internal) {
+      double s; int k;
+      if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
+      else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
+      const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
+      const double d = qk - s;
+      const double d2 = d * d;
+      lb[lvl * QUERY_THREADS] = __double2float_rd(d2);
+      if (!(d2 > st.best)) pending |= 1u << lvl;
+      node = 2 * node + 1 + (qk < s ? 0 : 1);
+      ++lvl;
+    }
+    scan_leaf(t, node, qx, qy, qz, st);
+  }
+  return st.besti;
 }
 
 // iu_get_cell_through_neighbors (:667-725) + get_cell_intersection (:729-764).
@@ -377,15 +415,15 @@ __device__ __forceinline__ void walk_ray(const double* __restrict__ rec, V3 r0, 
     const double* R = rec + (size_t)(ic1 - 1) * L::STRIDE;
     double face_distance = HUGE_DISTANCE;
     int i_face = -1;
+    // All faces are evaluated without branching (a division whose face fails `pdn > 0` is simply
+    // discarded): the same operations as :744-760 for the faces that count, and no divergence
+    // between lanes whose rays leave through different faces.
 #pragma unroll
     for (int k = 0; k < PPC; ++k) {
-      const V3 fn = ld3(R + L::NRM + 3 * k);
+      const V3 fn = ld3(R + L::NRM + 3 * k), rf = ld3(R + L::PTS + 3 * k);
       const double pdn = dot3(u, fn);
-      if (pdn > 0) {
-        const V3 rf = ld3(R + L::PTS + 3 * k);
-        const double dist = dot3(rf - r_p, fn) / pdn;
-        if (dist < face_distance) { face_distance = dist; i_face = k; }
-      }
+      const double dist = dot3(rf - r_p, fn) / pdn;
+      if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = k; }
     }
     r_p = {r_p.x + face_distance * u.x, r_p.y + face_distance * u.y, r_p.z + face_distance * u.z};   // :762
     distance_left = distance_left - face_distance;
@@ -488,11 +526,12 @@ struct QueryKernelParams {
 // THE hot kernel.  Persistent CTAs (grid = SMs x resident CTAs); the top tree levels live in
 // shared memory; one query per thread, processed in Morton order through `perm`.
 template <int CT, int MODE, int NV>
-__global__ void __launch_bounds__(QUERY_THREADS) k_query(const QueryKernelParams P) {
+__global__ void __launch_bounds__(QUERY_THREADS, 4) k_query(const QueryKernelParams P) {
   constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
   using L = RecLayout<PPC>;
   __shared__ double s_split[MAX_SM_NODES];
   __shared__ uint8_t s_dim[MAX_SM_NODES + 1];
+  extern __shared__ float s_lb[];   // [tree depth][QUERY_THREADS] plane-distance lower bounds (nearest_center)
   if (MODE != QM_INTERP_ICELL) {
     for (int i = threadIdx.x; i < P.tree.n_sm_nodes; i += blockDim.x) { s_split[i] = P.tree.split[i]; s_dim[i] = P.tree.sdim[i]; }
     __syncthreads();
@@ -502,7 +541,7 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_query(const QueryKernelParams
     const double qx = __ldg(P.r + 3 * i), qy = __ldg(P.r + 3 * i + 1), qz = __ldg(P.r + 3 * i + 2);
     int ic;   // 1-based device id of the containing cell, or <= 0
     if (MODE == QM_NEAREST) {
-      const int slot = nearest_center(P.tree, s_split, s_dim, qx, qy, qz);
+      const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
       P.out_i32[i] = slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0;
       continue;
     } else if (MODE == QM_INTERP_ICELL) {
@@ -515,7 +554,7 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_query(const QueryKernelParams
       if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }   // error stop, :490
       int start;
       if (h < 1) {                                                                      // :422-423
-        const int slot = nearest_center(P.tree, s_split, s_dim, qx, qy, qz);
+        const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
         if (slot < 0) { P.i_cell[i] = 0; atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
         start = slot + 1;
       } else {
@@ -597,7 +636,7 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_walk(const double* __restrict
   }
 }
 
-int query_grid_blocks(const void* kernel) {
+int sm_count() {
   static int n_sm = 0;
   if (n_sm == 0) {
     int dev = 0;
@@ -605,45 +644,57 @@ int query_grid_blocks(const void* kernel) {
     cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     if (n_sm <= 0) n_sm = 148;
   }
+  return n_sm;
+}
+
+// persistent grid: SMs x resident CTAs for this kernel and dynamic shared memory size
+int query_grid_blocks(const void* kernel, size_t dyn_smem) {
   int per_sm = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QUERY_THREADS, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QUERY_THREADS, dyn_smem);
   if (per_sm < 1) per_sm = 1;
-  return n_sm * per_sm;
+  return sm_count() * per_sm;
 }
 
 template <int CT, int MODE, int NV>
-void launch_query_inst(const QueryKernelParams& P, cudaStream_t s) {
+void launch_query_inst(const QueryKernelParams& P, int depth, cudaStream_t s) {
+  const size_t dyn = MODE == QM_INTERP_ICELL ? 0 : (size_t)(depth > 0 ? depth : 1) * QUERY_THREADS * sizeof(float);
   static int blocks = 0;
-  if (blocks == 0) blocks = query_grid_blocks((const void*)k_query<CT, MODE, NV>);
+  static size_t blocks_dyn = ~(size_t)0;
+  if (blocks == 0 || blocks_dyn != dyn) {
+    if (dyn + 20 * 1024 > 48 * 1024)
+      cudaFuncSetAttribute((const void*)k_query<CT, MODE, NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    blocks = query_grid_blocks((const void*)k_query<CT, MODE, NV>, dyn);
+    blocks_dyn = dyn;
+  }
   int64_t need = (P.n + QUERY_THREADS - 1) / QUERY_THREADS;
   int g = (int)(need < blocks ? need : blocks);
-  k_query<CT, MODE, NV><<<g, QUERY_THREADS, 0, s>>>(P);
+  k_query<CT, MODE, NV><<<g, QUERY_THREADS, dyn, s>>>(P);
 }
 
 template <int CT>
-void launch_query_ct(int mode, const QueryKernelParams& P, cudaStream_t s) {
+void launch_query_ct(int mode, const QueryKernelParams& P, int depth, cudaStream_t s) {
   switch (mode) {
-    case QM_NEAREST: launch_query_inst<CT, QM_NEAREST, 0>(P, s); break;
-    case QM_CELL: launch_query_inst<CT, QM_CELL, 0>(P, s); break;
-    case QM_CELL_F64: launch_query_inst<CT, QM_CELL_F64, 0>(P, s); break;
-    case QM_CELL_I32: launch_query_inst<CT, QM_CELL_I32, 0>(P, s); break;
+    case QM_NEAREST: launch_query_inst<CT, QM_NEAREST, 0>(P, depth, s); break;
+    case QM_CELL: launch_query_inst<CT, QM_CELL, 0>(P, depth, s); break;
+    case QM_CELL_F64: launch_query_inst<CT, QM_CELL_F64, 0>(P, depth, s); break;
+    case QM_CELL_I32: launch_query_inst<CT, QM_CELL_I32, 0>(P, depth, s); break;
     case QM_INTERP:
       switch (P.n_vars) {
-        case 1: launch_query_inst<CT, QM_INTERP, 1>(P, s); break;
-        case 2: launch_query_inst<CT, QM_INTERP, 2>(P, s); break;
-        case 3: launch_query_inst<CT, QM_INTERP, 3>(P, s); break;
-        case 4: launch_query_inst<CT, QM_INTERP, 4>(P, s); break;
-        case 8: launch_query_inst<CT, QM_INTERP, 8>(P, s); break;
-        default: launch_query_inst<CT, QM_INTERP, 0>(P, s); break;
+        case 1: launch_query_inst<CT, QM_INTERP, 1>(P, depth, s); break;
+        case 2: launch_query_inst<CT, QM_INTERP, 2>(P, depth, s); break;
+        case 3: launch_query_inst<CT, QM_INTERP, 3>(P, depth, s); break;
+        case 4: launch_query_inst<CT, QM_INTERP, 4>(P, depth, s); break;
+        case 8: launch_query_inst<CT, QM_INTERP, 8>(P, depth, s); break;
+        default: launch_query_inst<CT, QM_INTERP, 0>(P, depth, s); break;
       }
       break;
     case QM_INTERP_ICELL:
       switch (P.n_vars) {
-        case 1: launch_query_inst<CT, QM_INTERP_ICELL, 1>(P, s); break;
-        case 2: launch_query_inst<CT, QM_INTERP_ICELL, 2>(P, s); break;
-        case 3: launch_query_inst<CT, QM_INTERP_ICELL, 3>(P, s); break;
-        case 4: launch_query_inst<CT, QM_INTERP_ICELL, 4>(P, s); break;
-        default: launch_query_inst<CT, QM_INTERP_ICELL, 0>(P, s); break;
+        case 1: launch_query_inst<CT, QM_INTERP_ICELL, 1>(P, depth, s); break;
+        case 2: launch_query_inst<CT, QM_INTERP_ICELL, 2>(P, depth, s); break;
+        case 3: launch_query_inst<CT, QM_INTERP_ICELL, 3>(P, depth, s); break;
+        case 4: launch_query_inst<CT, QM_INTERP_ICELL, 4>(P, depth, s); break;
+        default: launch_query_inst<CT, QM_INTERP_ICELL, 0>(P, depth, s); break;
       }
       break;
   }
@@ -771,9 +822,9 @@ int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
   P.n = a.n; P.n_cells = g.n_cells; P.pd_stride = g.pd_stride; P.n_vars = a.n_vars; P.max_steps = a.max_steps;
   for (int v = 0; v < MAX_VARS; ++v) P.ivars[v] = a.ivars[v];
-  if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, s);
-  else if (g.cell_type == IU_QUAD_CT) launch_query_ct<IU_QUAD_CT>(a.mode, P, s);
-  else launch_query_ct<IU_TETRA_CT>(a.mode, P, s);
+  if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, g.depth, s);
+  else if (g.cell_type == IU_QUAD_CT) launch_query_ct<IU_QUAD_CT>(a.mode, P, g.depth, s);
+  else launch_query_ct<IU_TETRA_CT>(a.mode, P, g.depth, s);
   return 1;
 }
 
@@ -781,7 +832,7 @@ int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   const int32_t* mask = a.mask_col >= 0 ? g.icd + (size_t)a.mask_col * g.n_cells : nullptr;
   const int64_t need = (a.n + QUERY_THREADS - 1) / QUERY_THREADS;
-  const int b = (int)(need < 148 * 8 ? need : 148 * 8);
+  const int b = (int)(need < sm_count() * 8 ? need : sm_count() * 8);
   if (g.ppc == 3) k_walk<3><<<b, QUERY_THREADS, 0, s>>>(g.rec, g.dev_of_orig, g.orig_of_dev, mask, g.n_cells, g.counters, a);
   else k_walk<4><<<b, QUERY_THREADS, 0, s>>>(g.rec, g.dev_of_orig, g.orig_of_dev, mask, g.n_cells, g.counters, a);
   return 1;
