@@ -2,7 +2,7 @@
 # Round profile recipe (run under gpurun): GPU parity tests, the default bench line, then the two
 # ncu passes of /opt/skills/guides/B200_PROFILING.md on a shortened bench command.
 # usage: tools/profile.sh [tag]   -> everything lands in gpurun_out/<tag>_*
-tag=${1:-r01}
+tag=${1:-r01b}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/${tag}_smi.csv 2>&1
 nproc > gpurun_out/${tag}_nproc.txt
