@@ -54,6 +54,8 @@ extern "C" {
 #define IU_B200_OPT_HOST_CHUNK 3    /* queries per H2D/compute/D2H pipeline chunk (host API)      */
 #define IU_B200_OPT_DEV_BATCH 4     /* max queries per internal device sub-batch (workspace bound) */
 #define IU_B200_OPT_TIME_KERNELS 5  /* 1: bracket the hot kernel and the sort with CUDA events (stats 7..9) */
+#define IU_B200_OPT_DYNAMIC_TILES 6 /* 1 (default): sorted batches are handed to warps as tiles of consecutive
+                                       queries from a device ticket counter; 0: static grid-stride assignment */
 
 /* indices into the int64 array filled by iu_b200_get_stats */
 #define IU_B200_STAT_KERNEL_LAUNCHES 0 /* kernels of this library launched since creation/reset */

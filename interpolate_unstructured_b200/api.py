@@ -21,14 +21,15 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libiu_b200.so")
+# IU_B200_LIB selects an alternative build of the same CUDA library (kernel tuning experiments)
+LIB_PATH = os.environ.get("IU_B200_LIB") or os.path.join(_HERE, "lib", "libiu_b200.so")
 _lib = None
 
 TRIANGLE, QUAD, TETRA = 1, 2, 3
 CELL_TYPES = {"triangle": TRIANGLE, "quad": QUAD, "tetra": TETRA}
 E_INVAL, E_CUDA, E_IO, E_HINT, E_NOMEM = -1, -2, -3, -4, -5
 CELL_WALK_LIMIT = -2
-OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KERNELS = 1, 2, 3, 4, 5
+OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KERNELS, OPT_DYNAMIC_TILES = 1, 2, 3, 4, 5, 6
 STAT_NAMES = ["kernel_launches", "walk_limit_hits", "queries", "workspace_bytes", "mesh_bytes", "tree_depth",
               "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "reserved10", "reserved11"]
 

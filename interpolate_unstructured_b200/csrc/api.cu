@@ -86,6 +86,7 @@ struct iu_b200_grid {
   int64_t max_walk_steps = 1 << 20;
   int64_t host_chunk = 1 << 22;
   int64_t dev_batch = 1 << 26;
+  int dynamic_tiles = 1;   // sorted sub-batches draw tiles of queries from a ticket counter (kernels.cu, SCHED = 1)
   // stats
   int64_t n_launches = 0, n_queries = 0;
   size_t mesh_bytes = 0;
@@ -99,7 +100,7 @@ struct iu_b200_grid {
   unsigned long long* h_counters = nullptr;   // pinned, N_SLOTS x CNT_N snapshots
   void* h_stage = nullptr;                     // pinned staging for the rare "merge" path
   size_t h_stage_bytes = 0;
-  unsigned long long seen[CNT_N] = {0, 0, 0, 0};   // counter values already accounted for
+  unsigned long long seen[CNT_N] = {0};   // counter values already accounted for
   // optional per-kernel timing (IU_B200_OPT_TIME_KERNELS): event pairs around the hot kernel and the sort
   bool time_kernels = false;
   struct Timed { cudaEvent_t a, b; int kind; };
@@ -167,7 +168,7 @@ void collect_timings(iu_b200_grid* g) {
 }
 
 void free_device_grid(DeviceGrid& d) {
-  cudaFree(d.split); cudaFree(d.sdim); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
+  cudaFree(d.node); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
   cudaFree(d.orig_of_dev); cudaFree(d.pd); cudaFree(d.cd); cudaFree(d.icd); cudaFree(d.counters);
   d = DeviceGrid();
 }
@@ -265,8 +266,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     for (int l = 1; l < tree.n_leaves; l <<= 1) ++g->tree_depth;
     d.depth = g->tree_depth;
     const size_t n_slots = (size_t)tree.n_leaves * LEAF;
-    CU(cudaMalloc((void**)&d.split, std::max<size_t>(1, d.n_internal) * 8));
-    CU(cudaMalloc((void**)&d.sdim, std::max<size_t>(1, d.n_internal)));
+    CU(cudaMalloc((void**)&d.node, std::max<size_t>(1, d.n_internal) * sizeof(double2)));
     CU(cudaMalloc((void**)&d.orig_of_dev, n_slots * 4));
     CU(cudaMalloc((void**)&d.dev_of_orig, ((size_t)n_cells + 1) * 4));
     CU(cudaMalloc((void**)&d.centers4, n_slots * 32));
@@ -275,8 +275,15 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     CU(cudaMemsetAsync(d.counters, 0, CNT_N * sizeof(unsigned long long), s));
     CU(cudaMemsetAsync(d.dev_of_orig, 0, ((size_t)n_cells + 1) * 4, s));
     if (d.n_internal > 0) {
-      CU(cudaMemcpyAsync(d.split, tree.split.data(), (size_t)d.n_internal * 8, cudaMemcpyHostToDevice, s));
-      CU(cudaMemcpyAsync(d.sdim, tree.sdim.data(), (size_t)d.n_internal, cudaMemcpyHostToDevice, s));
+      // interleave {split, bits(dim)}: one 16-byte load per tree level on the device
+      std::vector<double2> nodes((size_t)d.n_internal);
+      for (int i = 0; i < d.n_internal; ++i) {
+        const long long dim = tree.sdim[i];
+        double bits;
+        std::memcpy(&bits, &dim, 8);
+        nodes[i] = make_double2(tree.split[i], bits);
+      }
+      CU(cudaMemcpy(d.node, nodes.data(), nodes.size() * sizeof(double2), cudaMemcpyHostToDevice));
     }
     CU(cudaMemcpyAsync(d.orig_of_dev, tree.orig_of_slot.data(), n_slots * 4, cudaMemcpyHostToDevice, s));
     g->n_launches += launch_build_records(d, d_points.p, d_cells.p, d_neigh.p, d_centers.p, s);
@@ -303,7 +310,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 9 +
+    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 16 +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));
@@ -599,6 +606,10 @@ int iu_b200_set_option(iu_b200_grid* g, int option, int64_t value) {
       if (value < 1 || value > (1LL << 31)) break;
       g->dev_batch = value;
       return IU_B200_OK;
+    case IU_B200_OPT_DYNAMIC_TILES:
+      if (value < 0 || value > 1) break;
+      g->dynamic_tiles = (int)value;
+      return IU_B200_OK;
     case IU_B200_OPT_TIME_KERNELS:
       if (value < 0 || value > 1) break;
       g->time_kernels = value != 0;
@@ -693,6 +704,7 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
                                           g->sort_temp.p, g->sort_temp.n, nullptr, s);
       ts.stop();
       b.perm = g->idx_alt.p;
+      b.dynamic = g->dynamic_tiles != 0;
     }
     TimedScope tq(g, s, 0);
     g->n_launches += launch_query(g->dg, b, s);

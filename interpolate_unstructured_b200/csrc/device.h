@@ -33,15 +33,14 @@ enum QueryMode : int {
 };
 
 // counters (device, unsigned long long each)
-enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_EARLY = 3, CNT_N = 4 };
+enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_EARLY = 3, CNT_TICKET = 4, CNT_N = 5 };
 
 struct DeviceGrid {
   int cell_type = 0, ppc = 0, n_cells = 0, n_points = 0;
   // kd-tree
   int n_leaves = 0, n_internal = 0, n_sm_nodes = 0;
   int depth = 0;                   // levels of internal nodes = level of the deepest leaf
-  double* split = nullptr;
-  uint8_t* sdim = nullptr;
+  double2* node = nullptr;         // n_internal x {split value, bits(split dimension)}, heap order
   double* centers4 = nullptr;      // n_leaves*LEAF x {x, y, z, bits(original id)}; padding = +inf
   // mesh
   double* rec = nullptr;           // n_leaves*LEAF records
@@ -69,6 +68,7 @@ struct QueryArgs {
   int n_vars = 0;
   int ivars[MAX_VARS] = {0};        // 0-based columns
   int max_steps = 1 << 20;
+  bool dynamic = false;             // draw tiles of consecutive queries from a ticket counter (large sorted batches)
 };
 
 struct WalkArgs {

@@ -25,7 +25,23 @@ namespace {
 constexpr double TINY_DISTANCE = 1e-100;   // m_interp_unstructured.f90:20
 constexpr double HUGE_DISTANCE = 1e100;    // :738
 constexpr int QUERY_THREADS = 256;
+#ifndef IU_QUERY_MIN_BLOCKS
+#define IU_QUERY_MIN_BLOCKS 4   // resident CTAs per SM the hot kernel is compiled for (64 registers per thread)
+#endif
 constexpr int MAX_SM_NODES = 2047;         // top 11 tree levels staged in shared memory
+
+// Query inputs and results are touched exactly once per launch: mark them evict-first (ld/st .cs)
+// so that they do not push the cell records of the current Morton window out of L2.
+#ifndef IU_STREAM_HINTS
+#define IU_STREAM_HINTS 1
+#endif
+#if IU_STREAM_HINTS
+#define LD_STREAM(p) __ldcs(p)
+#define ST_STREAM(p, v) __stcs(p, v)
+#else
+#define LD_STREAM(p) (*(p))
+#define ST_STREAM(p, v) (*(p) = (v))
+#endif
 
 struct V3 { double x, y, z; };
 __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
@@ -65,6 +81,19 @@ __device__ __forceinline__ double norm2_3(V3 v) {
 }
 
 __device__ __forceinline__ V3 ld3(const double* p) { return {__ldg(p), __ldg(p + 1), __ldg(p + 2)}; }
+
+// PPC consecutive (x, y, z) triples starting at the 16-byte aligned address p, fetched as 16-byte
+// loads (PPC = 3 reads one trailing double that belongs to the record: area / pad)
+template <int PPC>
+__device__ __forceinline__ void ld3n(const double* p, V3* out) {
+  constexpr int N2 = (3 * PPC + 1) / 2;
+  double d[2 * N2];
+  const double2* p2 = reinterpret_cast<const double2*>(p);
+#pragma unroll
+  for (int j = 0; j < N2; ++j) { const double2 v = __ldg(p2 + j); d[2 * j] = v.x; d[2 * j + 1] = v.y; }
+#pragma unroll
+  for (int k = 0; k < PPC; ++k) out[k] = V3{d[3 * k], d[3 * k + 1], d[3 * k + 2]};
+}
 
 // ------------------------------------------------------------------------------------------------
 // set-up kernels
@@ -288,8 +317,7 @@ __global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lo
 // device-side pieces of the hot path
 // ------------------------------------------------------------------------------------------------
 struct TreeView {
-  const double* split;
-  const uint8_t* sdim;
+  const double2* node;   // {split value, bits(split dimension)} per internal node, heap order
   const double* centers4;
   int n_internal;
   int n_sm_nodes;
@@ -348,7 +376,7 @@ __device__ __forceinline__ int nearest_center(const TreeView& t, const double* s
   while (node < t.n_internal) {
     double s; int k;
     if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
-    else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
+    else { const double2 nd = __ldg(t.node + node); s = nd.x; k = __double2loint(nd.y); }
     const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
     const double d = qk - s;
     lb[lvl * QUERY_THREADS] = __double2float_rd(d * d);
@@ -380,7 +408,7 @@ __device__ __forceinline__ int nearest_center(const TreeView& t, const double* s
     while (node < t.n_internal) {
       double s; int k;
       if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
-      else { s = __ldg(t.split + node); k = __ldg(t.sdim + node); }
+      else { const double2 nd = __ldg(t.node + node); s = nd.x; k = __double2loint(nd.y); }
       const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
       const double d = qk - s;
       const double d2 = d * d;
@@ -418,12 +446,20 @@ __device__ __forceinline__ void walk_ray(const double* __restrict__ rec, V3 r0, 
     // All faces are evaluated without branching (a division whose face fails `pdn > 0` is simply
     // discarded): the same operations as :744-760 for the faces that count, and no divergence
     // between lanes whose rays leave through different faces.
+    // faces two at a time: 6 + 6 doubles as 16-byte loads (bounded register footprint)
 #pragma unroll
-    for (int k = 0; k < PPC; ++k) {
-      const V3 fn = ld3(R + L::NRM + 3 * k), rf = ld3(R + L::PTS + 3 * k);
-      const double pdn = dot3(u, fn);
-      const double dist = dot3(rf - r_p, fn) / pdn;
-      if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = k; }
+    for (int h = 0; h < PPC; h += 2) {
+      V3 fn[2], rf[2];
+      if (h + 1 < PPC) { ld3n<2>(R + L::NRM + 3 * h, fn); ld3n<2>(R + L::PTS + 3 * h, rf); }
+      else { ld3n<1>(R + L::NRM + 3 * h, fn); ld3n<1>(R + L::PTS + 3 * h, rf); }
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        if (h + j < PPC) {
+          const double pdn = dot3(u, fn[j]);
+          const double dist = dot3(rf[j] - r_p, fn[j]) / pdn;
+          if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = h + j; }
+        }
+      }
     }
     r_p = {r_p.x + face_distance * u.x, r_p.y + face_distance * u.y, r_p.z + face_distance * u.z};   // :762
     distance_left = distance_left - face_distance;
@@ -520,42 +556,68 @@ struct QueryKernelParams {
   int pd_stride;
   int n_vars;
   int max_steps;
+  int pairs;                      // 1: variables (2j, 2j+1) of the request are adjacent, 16-byte aligned columns
+  unsigned long long* ticket;     // work counter of the dynamically scheduled variant (zeroed before the launch)
   int ivars[MAX_VARS];
 };
 
 // THE hot kernel.  Persistent CTAs (grid = SMs x resident CTAs); the top tree levels live in
 // shared memory; one query per thread, processed in Morton order through `perm`.
-template <int CT, int MODE, int NV>
-__global__ void __launch_bounds__(QUERY_THREADS, 4) k_query(const QueryKernelParams P) {
+// SCHED = 0: static grid-stride assignment.  SCHED = 1: every warp draws tiles of TILE consecutive
+// (sorted) queries from a global ticket counter, so that all queries in flight on the GPU stay
+// within one narrow window of the Morton order whatever the speed differences between warps and
+// SMs -- the window's cell records then fit in L2 and each is fetched from HBM about once.
+constexpr int TILE = 128;
+template <int CT, int MODE, int NV, int SCHED>
+__global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(const QueryKernelParams P) {
   constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
   using L = RecLayout<PPC>;
   __shared__ double s_split[MAX_SM_NODES];
   __shared__ uint8_t s_dim[MAX_SM_NODES + 1];
   extern __shared__ float s_lb[];   // [tree depth][QUERY_THREADS] plane-distance lower bounds (nearest_center)
   if (MODE != QM_INTERP_ICELL) {
-    for (int i = threadIdx.x; i < P.tree.n_sm_nodes; i += blockDim.x) { s_split[i] = P.tree.split[i]; s_dim[i] = P.tree.sdim[i]; }
+    for (int i = threadIdx.x; i < P.tree.n_sm_nodes; i += blockDim.x) {
+      const double2 nd = P.tree.node[i];
+      s_split[i] = nd.x; s_dim[i] = (uint8_t)__double2loint(nd.y);
+    }
     __syncthreads();
   }
-  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < P.n; t += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t i = P.perm ? (int64_t)__ldg(P.perm + t) : t;
-    const double qx = __ldg(P.r + 3 * i), qy = __ldg(P.r + 3 * i + 1), qz = __ldg(P.r + 3 * i + 2);
+  const int lane = threadIdx.x & 31;
+  int64_t t = SCHED ? 0 : (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t tile = 0;
+  int sub = TILE / 32;
+  for (;; t += (int64_t)gridDim.x * blockDim.x) {
+    if (SCHED) {
+      if (sub == TILE / 32) {
+        unsigned long long b = 0;
+        if (lane == 0) b = atomicAdd(P.ticket, (unsigned long long)TILE);
+        tile = (int64_t)__shfl_sync(0xffffffffu, b, 0);
+        sub = 0;
+      }
+      if (tile >= P.n) break;
+      t = tile + 32 * sub + lane;
+      ++sub;
+      if (t >= P.n) continue;
+    } else if (t >= P.n) break;
+    const int64_t i = P.perm ? (int64_t)LD_STREAM(P.perm + t) : t;
+    const double qx = LD_STREAM(P.r + 3 * i), qy = LD_STREAM(P.r + 3 * i + 1), qz = LD_STREAM(P.r + 3 * i + 2);
     int ic;   // 1-based device id of the containing cell, or <= 0
     if (MODE == QM_NEAREST) {
       const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
-      P.out_i32[i] = slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0;
+      ST_STREAM(P.out_i32 + i, slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0);
       continue;
     } else if (MODE == QM_INTERP_ICELL) {
-      const int h = P.i_cell[i];
+      const int h = LD_STREAM(P.i_cell + i);
       if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }
       if (h < 1) { atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
       ic = __ldg(P.dev_of_orig + h);
     } else {
-      const int h = P.i_cell[i];
+      const int h = LD_STREAM(P.i_cell + i);
       if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }   // error stop, :490
       int start;
       if (h < 1) {                                                                      // :422-423
         const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
-        if (slot < 0) { P.i_cell[i] = 0; atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
+        if (slot < 0) { ST_STREAM(P.i_cell + i, 0); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
         start = slot + 1;
       } else {
         start = __ldg(P.dev_of_orig + h);                                               // :424-426
@@ -568,46 +630,63 @@ __global__ void __launch_bounds__(QUERY_THREADS, 4) k_query(const QueryKernelPar
         ic = IU_WALK_LIMIT;
         atomicAdd(P.counters + CNT_WALK_LIMIT, 1ULL);
       }
-      if (ic < 1) { P.i_cell[i] = ic; atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }   // :492
+      if (ic < 1) { ST_STREAM(P.i_cell + i, ic); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }   // :492
     }
     const double* R = P.rec + (size_t)(ic - 1) * L::STRIDE;
     const int32_t* RI = reinterpret_cast<const int32_t*>(R);
     const int orig = __ldg(RI + L::ORG_I);
-    if (MODE != QM_INTERP_ICELL) P.i_cell[i] = orig;
+    if (MODE != QM_INTERP_ICELL) ST_STREAM(P.i_cell + i, orig);
     if (MODE == QM_CELL_F64) {
-      P.out_f64[i] = __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1));          // :447
+      ST_STREAM(P.out_f64 + i, __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));          // :447
     } else if (MODE == QM_CELL_I32) {
-      P.out_i32[i] = __ldg(P.icd + (size_t)P.ivars[0] * P.n_cells + (orig - 1));         // :461
+      ST_STREAM(P.out_i32 + i, __ldg(P.icd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));         // :461
     } else if (MODE == QM_INTERP || MODE == QM_INTERP_ICELL) {                           // :498-527
       V3 p[PPC];
-      int pid[PPC];
-#pragma unroll
-      for (int k = 0; k < PPC; ++k) { p[k] = ld3(R + L::PTS + 3 * k); pid[k] = __ldg(RI + L::CEL_I + k); }
+      int pid[4];
+      ld3n<PPC>(R + L::PTS, p);
+      {
+        const int4 c = __ldg(reinterpret_cast<const int4*>(RI + L::CEL_I));
+        pid[0] = c.x; pid[1] = c.y; pid[2] = c.z; pid[3] = c.w;
+      }
       Weights<CT> W;
       W.setup(p, __ldg(R + L::VOL), V3{qx, qy, qz});
       double* out = P.out_f64 + (size_t)i * P.n_vars;
       if (NV > 0) {
         double res[NV > 0 ? NV : 1];
+        if (NV % 2 == 0 && P.pairs) {   // adjacent column pairs: one 16-byte load per vertex and pair
 #pragma unroll
-        for (int v = 0; v < NV; ++v) {
-          double d[4];
+          for (int v = 0; v < NV; v += 2) {
+            double d0[4], d1[4];
 #pragma unroll
-          for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
-          res[v] = W.apply(d);
+            for (int k = 0; k < PPC; ++k) {
+              const double2 x = __ldg(reinterpret_cast<const double2*>(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]));
+              d0[k] = x.x; d1[k] = x.y;
+            }
+            res[v] = W.apply(d0);
+            res[v + 1] = W.apply(d1);
+          }
+        } else {
+#pragma unroll
+          for (int v = 0; v < NV; ++v) {
+            double d[4];
+#pragma unroll
+            for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
+            res[v] = W.apply(d);
+          }
         }
         if (NV % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
 #pragma unroll
-          for (int v = 0; v < NV; v += 2) *reinterpret_cast<double2*>(out + v) = make_double2(res[v], res[v + 1]);
+          for (int v = 0; v < NV; v += 2) ST_STREAM(reinterpret_cast<double2*>(out + v), make_double2(res[v], res[v + 1]));
         } else {
 #pragma unroll
-          for (int v = 0; v < NV; ++v) out[v] = res[v];
+          for (int v = 0; v < NV; ++v) ST_STREAM(out + v, res[v]);
         }
       } else {
         for (int v = 0; v < P.n_vars; ++v) {
           double d[4];
 #pragma unroll
           for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
-          out[v] = W.apply(d);
+          ST_STREAM(out + v, W.apply(d));
         }
       }
     }
@@ -655,20 +734,28 @@ int query_grid_blocks(const void* kernel, size_t dyn_smem) {
   return sm_count() * per_sm;
 }
 
-template <int CT, int MODE, int NV>
-void launch_query_inst(const QueryKernelParams& P, int depth, cudaStream_t s) {
+template <int CT, int MODE, int NV, int SCHED>
+void launch_query_sched(const QueryKernelParams& P, int depth, cudaStream_t s) {
   const size_t dyn = MODE == QM_INTERP_ICELL ? 0 : (size_t)(depth > 0 ? depth : 1) * QUERY_THREADS * sizeof(float);
   static int blocks = 0;
   static size_t blocks_dyn = ~(size_t)0;
   if (blocks == 0 || blocks_dyn != dyn) {
     if (dyn + 20 * 1024 > 48 * 1024)
-      cudaFuncSetAttribute((const void*)k_query<CT, MODE, NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-    blocks = query_grid_blocks((const void*)k_query<CT, MODE, NV>, dyn);
+      cudaFuncSetAttribute((const void*)k_query<CT, MODE, NV, SCHED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    blocks = query_grid_blocks((const void*)k_query<CT, MODE, NV, SCHED>, dyn);
     blocks_dyn = dyn;
   }
   int64_t need = (P.n + QUERY_THREADS - 1) / QUERY_THREADS;
   int g = (int)(need < blocks ? need : blocks);
-  k_query<CT, MODE, NV><<<g, QUERY_THREADS, dyn, s>>>(P);
+  if (SCHED) cudaMemsetAsync(P.ticket, 0, sizeof(unsigned long long), s);
+  k_query<CT, MODE, NV, SCHED><<<g, QUERY_THREADS, dyn, s>>>(P);
+}
+
+// dynamic tiles pay off once a batch is large and sorted; small batches keep the static assignment
+template <int CT, int MODE, int NV>
+void launch_query_inst(const QueryKernelParams& P, int depth, cudaStream_t s) {
+  if (P.ticket) launch_query_sched<CT, MODE, NV, 1>(P, depth, s);
+  else launch_query_sched<CT, MODE, NV, 0>(P, depth, s);
 }
 
 template <int CT>
@@ -816,12 +903,19 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   QueryKernelParams P;
-  P.tree = TreeView{g.split, g.sdim, g.centers4, g.n_internal, g.n_sm_nodes};
+  P.tree = TreeView{g.node, g.centers4, g.n_internal, g.n_sm_nodes};
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
   P.n = a.n; P.n_cells = g.n_cells; P.pd_stride = g.pd_stride; P.n_vars = a.n_vars; P.max_steps = a.max_steps;
   for (int v = 0; v < MAX_VARS; ++v) P.ivars[v] = a.ivars[v];
+  P.pairs = 0;
+  if ((a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL) && a.n_vars % 2 == 0 && g.pd_stride % 2 == 0) {
+    P.pairs = 1;
+    for (int v = 0; v < a.n_vars; v += 2)
+      if (a.ivars[v] % 2 != 0 || a.ivars[v + 1] != a.ivars[v] + 1) P.pairs = 0;
+  }
+  P.ticket = a.dynamic ? g.counters + CNT_TICKET : nullptr;
   if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, g.depth, s);
   else if (g.cell_type == IU_QUAD_CT) launch_query_ct<IU_QUAD_CT>(a.mode, P, g.depth, s);
   else launch_query_ct<IU_TETRA_CT>(a.mode, P, g.depth, s);
