@@ -704,7 +704,7 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
                                           g->sort_temp.p, g->sort_temp.n, nullptr, s);
       ts.stop();
       b.perm = g->idx_alt.p;
-      b.dynamic = g->dynamic_tiles != 0;
+      b.dynamic = g->dynamic_tiles;
     }
     TimedScope tq(g, s, 0);
     g->n_launches += launch_query(g->dg, b, s);

@@ -68,7 +68,7 @@ struct QueryArgs {
   int n_vars = 0;
   int ivars[MAX_VARS] = {0};        // 0-based columns
   int max_steps = 1 << 20;
-  bool dynamic = false;             // draw tiles of consecutive queries from a ticket counter (large sorted batches)
+  int dynamic = 0;                  // 1: draw tiles of consecutive queries from a ticket counter (sorted batches only)
 };
 
 struct WalkArgs {

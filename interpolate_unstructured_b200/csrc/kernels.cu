@@ -32,6 +32,9 @@ constexpr int MAX_SM_NODES = 2047;         // top 11 tree levels staged in share
 
 // Query inputs and results are touched exactly once per launch: mark them evict-first (ld/st .cs)
 // so that they do not push the cell records of the current Morton window out of L2.
+#ifndef IU_WALK_256
+#define IU_WALK_256 0   // 1: 32-byte loads in the walk too (6 instead of 12 per cell, but spills at 64 registers: slower)
+#endif
 #ifndef IU_STREAM_HINTS
 #define IU_STREAM_HINTS 1
 #endif
@@ -81,6 +84,20 @@ __device__ __forceinline__ double norm2_3(V3 v) {
 }
 
 __device__ __forceinline__ V3 ld3(const double* p) { return {__ldg(p), __ldg(p + 1), __ldg(p + 2)}; }
+
+// 32-byte load (sm_100a: LDG.E.256): one L1 tag lookup per lane for a whole leaf slot / a third of
+// a record's normals instead of two.  p must be 32-byte aligned.
+struct D4 { double x, y, z, w; };
+__device__ __forceinline__ D4 ld256(const double* p) {
+  D4 r;
+  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+  return r;
+}
+// 4 consecutive (x, y, z) triples at a 32-byte aligned address as three 32-byte loads
+__device__ __forceinline__ void ld3x4(const double* p, V3* out) {
+  const D4 a = ld256(p), b = ld256(p + 4), c = ld256(p + 8);
+  out[0] = V3{a.x, a.y, a.z}; out[1] = V3{a.w, b.x, b.y}; out[2] = V3{b.z, b.w, c.x}; out[3] = V3{c.y, c.z, c.w};
+}
 
 // PPC consecutive (x, y, z) triples starting at the 16-byte aligned address p, fetched as 16-byte
 // loads (PPC = 3 reads one trailing double that belongs to the record: area / pad)
@@ -346,19 +363,19 @@ struct NNState {
 };
 
 __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx, double qy, double qz, NNState& st) {
-  // two batches of four slots (8 independent 16-B loads in flight each)
+  // two batches of four slots (4 independent 32-byte loads in flight each)
   const int base = (node - t.n_internal) * LEAF;
-  const double2* c = reinterpret_cast<const double2*>(t.centers4) + 2 * (size_t)base;
+  const double* c = t.centers4 + 4 * (size_t)base;
 #pragma unroll
   for (int h = 0; h < LEAF; h += 4) {
-    double2 a[4], b[4];
+    D4 a[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { a[j] = __ldg(c + 2 * (h + j)); b[j] = __ldg(c + 2 * (h + j) + 1); }
+    for (int j = 0; j < 4; ++j) a[j] = ld256(c + 4 * (h + j));
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const double dx = a[j].x - qx, dy = a[j].y - qy, dz = b[j].x - qz;
+      const double dx = a[j].x - qx, dy = a[j].y - qy, dz = a[j].z - qz;
       const double sd = (dx * dx + dy * dy) + dz * dz;
-      const long long o = __double_as_longlong(b[j].y);
+      const long long o = __double_as_longlong(a[j].w);
       // padding slots hold +inf centres (sd = inf or NaN): never selected because besti < 0 only
       // while best = +inf and 'sd < best' is false for them
       if (sd < st.best || (sd == st.best && o < st.besto && o > 0)) { st.best = sd; st.besti = base + h + j; st.besto = o; }
@@ -446,19 +463,38 @@ __device__ __forceinline__ void walk_ray(const double* __restrict__ rec, V3 r0, 
     // All faces are evaluated without branching (a division whose face fails `pdn > 0` is simply
     // discarded): the same operations as :744-760 for the faces that count, and no divergence
     // between lanes whose rays leave through different faces.
-    // faces two at a time: 6 + 6 doubles as 16-byte loads (bounded register footprint)
+    if (PPC == 4 && IU_WALK_256) {   // 96 + 96 bytes as six 32-byte loads
+      V3 fn[4], rf[4];
+      ld3x4(R + L::NRM, fn);
+      ld3x4(R + L::PTS, rf);
 #pragma unroll
-    for (int h = 0; h < PPC; h += 2) {
-      V3 fn[2], rf[2];
-      if (h + 1 < PPC) { ld3n<2>(R + L::NRM + 3 * h, fn); ld3n<2>(R + L::PTS + 3 * h, rf); }
-      else { ld3n<1>(R + L::NRM + 3 * h, fn); ld3n<1>(R + L::PTS + 3 * h, rf); }
+      for (int k = 0; k < 4; ++k) {
+        const double pdn = dot3(u, fn[k]);
+        const double dist = dot3(rf[k] - r_p, fn[k]) / pdn;
+        if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = k; }
+      }
+    } else if (PPC == 4) {           // faces two at a time: 6 + 6 doubles as 16-byte loads
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        if (h + j < PPC) {
+      for (int h = 0; h < 4; h += 2) {
+        V3 fn[2], rf[2];
+        ld3n<2>(R + L::NRM + 3 * h, fn);
+        ld3n<2>(R + L::PTS + 3 * h, rf);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
           const double pdn = dot3(u, fn[j]);
           const double dist = dot3(rf[j] - r_p, fn[j]) / pdn;
           if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = h + j; }
         }
+      }
+    } else {
+      V3 fn[3], rf[3];
+      ld3n<3>(R + L::NRM, fn);
+      ld3n<3>(R + L::PTS, rf);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const double pdn = dot3(u, fn[k]);
+        const double dist = dot3(rf[k] - r_p, fn[k]) / pdn;
+        if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = k; }
       }
     }
     r_p = {r_p.x + face_distance * u.x, r_p.y + face_distance * u.y, r_p.z + face_distance * u.z};   // :762
@@ -556,22 +592,119 @@ struct QueryKernelParams {
   int pd_stride;
   int n_vars;
   int max_steps;
-  int pairs;                      // 1: variables (2j, 2j+1) of the request are adjacent, 16-byte aligned columns
-  unsigned long long* ticket;     // work counter of the dynamically scheduled variant (zeroed before the launch)
+  int pairs;                      // 1 / 2: the requested variables come in adjacent, aligned groups of 2 / 4 columns
+  unsigned long long* ticket;     // work counter of the dynamically scheduled variants (zeroed before the launch)
+  int sched;
   int ivars[MAX_VARS];
 };
 
-// THE hot kernel.  Persistent CTAs (grid = SMs x resident CTAs); the top tree levels live in
-// shared memory; one query per thread, processed in Morton order through `perm`.
-// SCHED = 0: static grid-stride assignment.  SCHED = 1: every warp draws tiles of TILE consecutive
-// (sorted) queries from a global ticket counter, so that all queries in flight on the GPU stay
-// within one narrow window of the Morton order whatever the speed differences between warps and
-// SMs -- the window's cell records then fit in L2 and each is fetched from HBM about once.
-constexpr int TILE = 128;
-template <int CT, int MODE, int NV, int SCHED>
-__global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(const QueryKernelParams P) {
+__device__ __forceinline__ void load_node(const TreeView& t, const double* s_split, const uint8_t* s_dim, int node, double& s, int& k) {
+  if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
+  else { const double2 nd = __ldg(t.node + node); s = nd.x; k = __double2loint(nd.y); }
+}
+
+// Everything after the start cell is known: ray walk from the start cell's centre (iu_get_cell,
+// :429-432), then the mode's output.  `start` is a 1-based device id; for QM_INTERP_ICELL it is the
+// containing cell itself (no walk).
+template <int CT, int MODE, int NV>
+__device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t i, double qx, double qy, double qz, int start) {
   constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
   using L = RecLayout<PPC>;
+  int ic = start;
+  if (MODE != QM_INTERP_ICELL) {
+    const double* c4 = P.tree.centers4 + 4 * (size_t)(start - 1);
+    const V3 r0{__ldg(c4), __ldg(c4 + 1), __ldg(c4 + 2)};                             // :429
+    V3 r_p; int n_steps = 0, status; bool early;
+    walk_ray<PPC>(P.rec, r0, V3{qx, qy, qz}, start, P.max_steps, nullptr, ic, r_p, n_steps, status, early);
+    if (!early && n_steps > P.max_steps) {
+      ic = IU_WALK_LIMIT;
+      atomicAdd(P.counters + CNT_WALK_LIMIT, 1ULL);
+    }
+    if (ic < 1) { ST_STREAM(P.i_cell + i, ic); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); return; }   // :492
+  }
+  const double* R = P.rec + (size_t)(ic - 1) * L::STRIDE;
+  const int32_t* RI = reinterpret_cast<const int32_t*>(R);
+  const int orig = __ldg(RI + L::ORG_I);
+  if (MODE != QM_INTERP_ICELL) ST_STREAM(P.i_cell + i, orig);
+  if (MODE == QM_CELL_F64) {
+    ST_STREAM(P.out_f64 + i, __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));          // :447
+  } else if (MODE == QM_CELL_I32) {
+    ST_STREAM(P.out_i32 + i, __ldg(P.icd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));         // :461
+  } else if (MODE == QM_INTERP || MODE == QM_INTERP_ICELL) {                           // :498-527
+    V3 p[PPC];
+    int pid[4];
+    if (PPC == 4) ld3x4(R + L::PTS, p); else ld3n<PPC>(R + L::PTS, p);
+    {
+      const int4 c = __ldg(reinterpret_cast<const int4*>(RI + L::CEL_I));
+      pid[0] = c.x; pid[1] = c.y; pid[2] = c.z; pid[3] = c.w;
+    }
+    Weights<CT> W;
+    W.setup(p, __ldg(R + L::VOL), V3{qx, qy, qz});
+    double* out = P.out_f64 + (size_t)i * P.n_vars;
+    if (NV > 0) {
+      double res[NV > 0 ? NV : 1];
+      if (NV % 4 == 0 && P.pairs == 2) {   // aligned groups of four adjacent columns: one 32-byte load per vertex
+#pragma unroll
+        for (int v = 0; v < NV; v += 4) {
+          double d0[4], d1[4], d2[4], d3[4];
+#pragma unroll
+          for (int k = 0; k < PPC; ++k) {
+            const D4 x = ld256(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
+            d0[k] = x.x; d1[k] = x.y; d2[k] = x.z; d3[k] = x.w;
+          }
+          res[v] = W.apply(d0); res[v + 1] = W.apply(d1); res[v + 2] = W.apply(d2); res[v + 3] = W.apply(d3);
+        }
+      } else if (NV % 2 == 0 && P.pairs) {   // adjacent column pairs: one 16-byte load per vertex and pair
+#pragma unroll
+        for (int v = 0; v < NV; v += 2) {
+          double d0[4], d1[4];
+#pragma unroll
+          for (int k = 0; k < PPC; ++k) {
+            const double2 x = __ldg(reinterpret_cast<const double2*>(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]));
+            d0[k] = x.x; d1[k] = x.y;
+          }
+          res[v] = W.apply(d0);
+          res[v + 1] = W.apply(d1);
+        }
+      } else {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+          double d[4];
+#pragma unroll
+          for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
+          res[v] = W.apply(d);
+        }
+      }
+      if (NV % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+#pragma unroll
+        for (int v = 0; v < NV; v += 2) ST_STREAM(reinterpret_cast<double2*>(out + v), make_double2(res[v], res[v + 1]));
+      } else {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) ST_STREAM(out + v, res[v]);
+      }
+    } else {
+      for (int v = 0; v < P.n_vars; ++v) {
+        double d[4];
+#pragma unroll
+        for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
+        ST_STREAM(out + v, W.apply(d));
+      }
+    }
+  }
+}
+
+// THE hot kernel.  Persistent CTAs (grid = SMs x resident CTAs); the top tree levels live in
+// shared memory; one query per thread, processed in Morton order through `perm`.
+// SCHED = 0: static grid-stride assignment (unsorted batches).  SCHED = 1 (sorted batches): every
+// warp draws tiles of 128 consecutive sorted queries from a global ticket counter, so that all
+// queries in flight on the GPU stay within one narrow window of the Morton order whatever the
+// speed differences between warps and SMs.
+// Two designs that were built, measured on B200 and dropped (profiles/README.md): a three-phase
+// tiled kernel with a lane queue for the backtracking phase (fewer instructions, but the lost
+// intra-warp locality costs more L1 wavefronts than it saves), and a warp-packet kd-tree search
+// (uniform 32-byte loads still pay 8 LSU data-pipe wavefronts each for register write-back).
+template <int CT, int MODE, int NV, int SCHED>
+__global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(const QueryKernelParams P) {
   __shared__ double s_split[MAX_SM_NODES];
   __shared__ uint8_t s_dim[MAX_SM_NODES + 1];
   extern __shared__ float s_lb[];   // [tree depth][QUERY_THREADS] plane-distance lower bounds (nearest_center)
@@ -582,15 +715,17 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
     }
     __syncthreads();
   }
+  // SCHED = 1: warps draw STILE consecutive (sorted) queries at a time from the ticket counter
+  constexpr int STILE = 128;
   const int lane = threadIdx.x & 31;
   int64_t t = SCHED ? 0 : (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t tile = 0;
-  int sub = TILE / 32;
+  int sub = STILE / 32;
   for (;; t += (int64_t)gridDim.x * blockDim.x) {
     if (SCHED) {
-      if (sub == TILE / 32) {
+      if (sub == STILE / 32) {
         unsigned long long b = 0;
-        if (lane == 0) b = atomicAdd(P.ticket, (unsigned long long)TILE);
+        if (lane == 0) b = atomicAdd(P.ticket, (unsigned long long)STILE);
         tile = (int64_t)__shfl_sync(0xffffffffu, b, 0);
         sub = 0;
       }
@@ -601,95 +736,25 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
     } else if (t >= P.n) break;
     const int64_t i = P.perm ? (int64_t)LD_STREAM(P.perm + t) : t;
     const double qx = LD_STREAM(P.r + 3 * i), qy = LD_STREAM(P.r + 3 * i + 1), qz = LD_STREAM(P.r + 3 * i + 2);
-    int ic;   // 1-based device id of the containing cell, or <= 0
     if (MODE == QM_NEAREST) {
       const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
       ST_STREAM(P.out_i32 + i, slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0);
       continue;
-    } else if (MODE == QM_INTERP_ICELL) {
-      const int h = LD_STREAM(P.i_cell + i);
-      if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }
+    }
+    const int h = LD_STREAM(P.i_cell + i);
+    if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }     // error stop, :490
+    int start;
+    if (MODE == QM_INTERP_ICELL) {
       if (h < 1) { atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
-      ic = __ldg(P.dev_of_orig + h);
+      start = __ldg(P.dev_of_orig + h);
+    } else if (h < 1) {                                                                // :422-423
+      const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
+      if (slot < 0) { ST_STREAM(P.i_cell + i, 0); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
+      start = slot + 1;
     } else {
-      const int h = LD_STREAM(P.i_cell + i);
-      if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }   // error stop, :490
-      int start;
-      if (h < 1) {                                                                      // :422-423
-        const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
-        if (slot < 0) { ST_STREAM(P.i_cell + i, 0); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
-        start = slot + 1;
-      } else {
-        start = __ldg(P.dev_of_orig + h);                                               // :424-426
-      }
-      const double* c4 = P.tree.centers4 + 4 * (size_t)(start - 1);
-      const V3 r0{__ldg(c4), __ldg(c4 + 1), __ldg(c4 + 2)};                             // :429
-      V3 r_p; int n_steps = 0, status; bool early;
-      walk_ray<PPC>(P.rec, r0, V3{qx, qy, qz}, start, P.max_steps, nullptr, ic, r_p, n_steps, status, early);
-      if (!early && n_steps > P.max_steps) {
-        ic = IU_WALK_LIMIT;
-        atomicAdd(P.counters + CNT_WALK_LIMIT, 1ULL);
-      }
-      if (ic < 1) { ST_STREAM(P.i_cell + i, ic); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }   // :492
+      start = __ldg(P.dev_of_orig + h);                                                // :424-426
     }
-    const double* R = P.rec + (size_t)(ic - 1) * L::STRIDE;
-    const int32_t* RI = reinterpret_cast<const int32_t*>(R);
-    const int orig = __ldg(RI + L::ORG_I);
-    if (MODE != QM_INTERP_ICELL) ST_STREAM(P.i_cell + i, orig);
-    if (MODE == QM_CELL_F64) {
-      ST_STREAM(P.out_f64 + i, __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));          // :447
-    } else if (MODE == QM_CELL_I32) {
-      ST_STREAM(P.out_i32 + i, __ldg(P.icd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));         // :461
-    } else if (MODE == QM_INTERP || MODE == QM_INTERP_ICELL) {                           // :498-527
-      V3 p[PPC];
-      int pid[4];
-      ld3n<PPC>(R + L::PTS, p);
-      {
-        const int4 c = __ldg(reinterpret_cast<const int4*>(RI + L::CEL_I));
-        pid[0] = c.x; pid[1] = c.y; pid[2] = c.z; pid[3] = c.w;
-      }
-      Weights<CT> W;
-      W.setup(p, __ldg(R + L::VOL), V3{qx, qy, qz});
-      double* out = P.out_f64 + (size_t)i * P.n_vars;
-      if (NV > 0) {
-        double res[NV > 0 ? NV : 1];
-        if (NV % 2 == 0 && P.pairs) {   // adjacent column pairs: one 16-byte load per vertex and pair
-#pragma unroll
-          for (int v = 0; v < NV; v += 2) {
-            double d0[4], d1[4];
-#pragma unroll
-            for (int k = 0; k < PPC; ++k) {
-              const double2 x = __ldg(reinterpret_cast<const double2*>(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]));
-              d0[k] = x.x; d1[k] = x.y;
-            }
-            res[v] = W.apply(d0);
-            res[v + 1] = W.apply(d1);
-          }
-        } else {
-#pragma unroll
-          for (int v = 0; v < NV; ++v) {
-            double d[4];
-#pragma unroll
-            for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
-            res[v] = W.apply(d);
-          }
-        }
-        if (NV % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
-#pragma unroll
-          for (int v = 0; v < NV; v += 2) ST_STREAM(reinterpret_cast<double2*>(out + v), make_double2(res[v], res[v + 1]));
-        } else {
-#pragma unroll
-          for (int v = 0; v < NV; ++v) ST_STREAM(out + v, res[v]);
-        }
-      } else {
-        for (int v = 0; v < P.n_vars; ++v) {
-          double d[4];
-#pragma unroll
-          for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
-          ST_STREAM(out + v, W.apply(d));
-        }
-      }
-    }
+    finish_query<CT, MODE, NV>(P, i, qx, qy, qz, start);
   }
 }
 
@@ -735,7 +800,7 @@ int query_grid_blocks(const void* kernel, size_t dyn_smem) {
 }
 
 template <int CT, int MODE, int NV, int SCHED>
-void launch_query_sched(const QueryKernelParams& P, int depth, cudaStream_t s) {
+void launch_query_static(const QueryKernelParams& P, int depth, cudaStream_t s) {
   const size_t dyn = MODE == QM_INTERP_ICELL ? 0 : (size_t)(depth > 0 ? depth : 1) * QUERY_THREADS * sizeof(float);
   static int blocks = 0;
   static size_t blocks_dyn = ~(size_t)0;
@@ -751,11 +816,11 @@ void launch_query_sched(const QueryKernelParams& P, int depth, cudaStream_t s) {
   k_query<CT, MODE, NV, SCHED><<<g, QUERY_THREADS, dyn, s>>>(P);
 }
 
-// dynamic tiles pay off once a batch is large and sorted; small batches keep the static assignment
+// sched: 0 static grid-stride, 1 ticket tiles (sorted batches)
 template <int CT, int MODE, int NV>
 void launch_query_inst(const QueryKernelParams& P, int depth, cudaStream_t s) {
-  if (P.ticket) launch_query_sched<CT, MODE, NV, 1>(P, depth, s);
-  else launch_query_sched<CT, MODE, NV, 0>(P, depth, s);
+  if (P.ticket && P.perm && P.sched >= 1) launch_query_static<CT, MODE, NV, 1>(P, depth, s);
+  else launch_query_static<CT, MODE, NV, 0>(P, depth, s);
 }
 
 template <int CT>
@@ -914,8 +979,14 @@ int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
     P.pairs = 1;
     for (int v = 0; v < a.n_vars; v += 2)
       if (a.ivars[v] % 2 != 0 || a.ivars[v + 1] != a.ivars[v] + 1) P.pairs = 0;
+    if (P.pairs && a.n_vars % 4 == 0 && g.pd_stride % 4 == 0) {
+      P.pairs = 2;
+      for (int v = 0; v < a.n_vars; v += 4)
+        if (a.ivars[v] % 4 != 0 || a.ivars[v + 2] != a.ivars[v] + 2) P.pairs = 1;
+    }
   }
   P.ticket = a.dynamic ? g.counters + CNT_TICKET : nullptr;
+  P.sched = a.dynamic;
   if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, g.depth, s);
   else if (g.cell_type == IU_QUAD_CT) launch_query_ct<IU_QUAD_CT>(a.mode, P, g.depth, s);
   else launch_query_ct<IU_TETRA_CT>(a.mode, P, g.depth, s);

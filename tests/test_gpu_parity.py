@@ -346,3 +346,25 @@ def test_shuffled_cell_order_and_mid_size_mesh():
     assert np.abs(res[:, 0] - (r.sum(1) + 1)).max() < 1e-12
     st = g.stats()
     assert st["kernel_launches"] > 0 and st["walk_limit_hits"] == 0 and st["queries"] >= 2 * nq
+
+
+@pytest.mark.parametrize("kind,n", [("tetra", 24), ("quad", 200), ("triangle", 150)])
+def test_kernel_forms_agree_with_oracle(kind, n):
+    """IU_B200_OPT_DYNAMIC_TILES: static grid-stride and ticket-tile scheduling (dense, sparse and
+    tiny sorted batches; mixed cold / warm lanes) return the brute-force nearest centres and the
+    oracle's cells and values."""
+    g, o, pts = _both_from_mesh(kind, n, n_vars=4)
+    g.set_option(api.OPT_SORT_QUERIES, 1)
+    for nq, seed in ((200_000, 5), (3_000, 6), (33, 7)):
+        r = _queries(pts, nq, seed, shrink=-0.03)
+        oidx, best, second = o.nearest(r, "brute", nthreads=0)
+        ores, oic = o.interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -7.5), nn="brute", nthreads=0)
+        hint = np.where((np.arange(nq) % 3 == 0) & (oic >= 1), oic, 0).astype(np.int32)    # every third query warm
+        ohres, ohic = o.interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -7.5), i_cell=hint.copy(), nn="brute", nthreads=0)
+        for form in (0, 1):
+            g.set_option(api.OPT_DYNAMIC_TILES, form)
+            assert (g.find_nearby_cell_kdtree(r) == oidx).all(), (form, nq)
+            res, ic = g.iu_interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -7.5))
+            assert (ic == oic).all() and (res == ores).all(), (form, nq)
+            res, ic = g.iu_interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -7.5), i_cell=hint.copy())
+            assert (ic == ohic).all() and (res == ohres).all(), (form, nq)

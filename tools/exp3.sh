@@ -1,0 +1,16 @@
+#!/bin/bash
+# tiled kernel vs statically scheduled kernel; timing + DRAM bytes
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+B="python bench.py --queries 2e8 --steps 3 --warmup 2 --no-cpu --no-e2e"
+P="python bench.py --queries 2e8 --steps 1 --warmup 1 --no-cpu --no-e2e"
+M=dram__bytes_read.sum,dram__bytes_write.sum,lts__t_sector_hit_rate.pct,l1tex__t_sector_hit_rate.pct,gpu__time_duration.sum,smsp__thread_inst_executed_per_inst_executed.ratio,smsp__inst_executed.sum,l1tex__throughput.avg.pct_of_peak_sustained_elapsed,sm__warps_active.avg.pct_of_peak_sustained_active
+for dyn in 1 0; do
+  echo "== dynamic=$dyn"
+  $B --dynamic $dyn | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); r=d['roofline']
+print('value %.3e q/s  kernel %.2f ms/launch  share %.2f sort %.2f'%(d['value'], r['kernel_ms_per_launch'], r['kernel_share_of_step'], r['sort_share_of_step']))"
+  $P --dynamic $dyn > /dev/null 2>&1 && ncu --metrics $M --clock-control none -k regex:k_query -s 3 -c 1 --csv --log-file gpurun_out/exp3_${dyn}.csv $P --dynamic $dyn > /dev/null 2>&1
+  grep -E "dram__|hit_rate|time_duration|inst_executed|throughput|warps_active" gpurun_out/exp3_${dyn}.csv | awk -F'","' '{print "   ", $(NF-2), $(NF-1), $NF}'
+done 2>&1 | tee gpurun_out/exp3.txt
