@@ -528,6 +528,107 @@ bool point_is_inside_cell(const Grid& g, const double* r, int ic) {
   return true;
 }
 
+// iu_integrate_along_field, :989-1217 (Bogacki-Shampine RK3(2) along the interpolated field until
+// a boundary is reached).  The reference takes a user callback sub_int(ndim, nvar, field, y, dy_var)
+// (:61-74); a batched device version cannot call back into Fortran, so the integrand is one of
+//   0: none (nvar = 0)
+//   1: dy_var(:) = 1            -- arc length, exactly test_trace_field.f90:57-64
+//   2: dy_var(:) = norm2(field) -- potential-like line integral of |field|
+// y is (ndim+nvar, max_steps), y_field is (ndim, max_steps), both column-major as in Fortran.
+// i_icell_mask = 0 <=> both optional mask arguments absent.  boundary_material may be null.
+void sub_int_builtin(int integrand, int ndim, int nvar, const double* field, double* dy_var) {
+  double v = 1.0;
+  if (integrand == 2) v = norm2(V3{field[0], field[1], ndim > 2 ? field[2] : 0.0});
+  for (int i = 0; i < nvar; ++i) dy_var[i] = v;
+}
+
+void integrate_along_field(const Grid& g, int ndim, int nvar, int integrand, const int* i_field, double min_dx,
+                           double max_dx, int max_steps, double rtol, double atol, bool reverse, double* y,
+                           double* y_field, int& n_steps, bool axisymmetric, int i_icell_mask, int mask_value,
+                           int* boundary_material, int nn_mode) {
+  const double safety_fac = 0.8, inv_24 = 1 / 24.0, inv_9 = 1 / 9.0, min_radius = 1e-12, eps = 1e-8;
+  const int nt = ndim + nvar;
+  constexpr int MAXT = 8;
+  double ys[MAXT], y_2nd[MAXT], k[4][MAXT], field[3], scales[MAXT];
+  double r0[3] = {0, 0, 0}, r[3] = {0, 0, 0};
+  V3 r_p{0, 0, 0};
+  auto Y = [&](int i, int step) -> double& { return y[(size_t)(step - 1) * nt + i]; };         // y(i+1, step)
+  auto YF = [&](int i, int step) -> double& { return y_field[(size_t)(step - 1) * ndim + i]; };
+  auto mask_of = [&](int ic) { return g.icell_data[(size_t)(i_icell_mask - 1) * g.n_cells + (ic - 1)]; };
+  auto set_boundary = [&](int ic) {
+    if (boundary_material) *boundary_material = ic <= 0 ? -1 : mask_of(ic);                      // :1062-1068, :1087-1093
+  };
+  auto unitvec = [&](const double* f, double* out) {                                             // get_unitvec, :1192-1201
+    const double nrm = norm2(V3{f[0], f[1], ndim > 2 ? f[2] : 0.0});
+    for (int i = 0; i < ndim; ++i) { out[i] = f[i] / nrm; if (reverse) out[i] = -out[i]; }
+  };
+  n_steps = 1;
+  for (int i = 0; i < ndim; ++i) r0[i] = Y(i, 1);
+  int last_rejected = -100;
+  double dx = max_dx;
+  int i_cell = 0;
+  // field at the initial point: iu_interpolate_at, cold (:1054)
+  get_cell(g, r0, i_cell, nn_mode, nullptr, nullptr);
+  if (i_cell > 0) interpolate_at_icell(g, r0, ndim, i_field, field, i_cell);
+  bool valid = i_cell > 0 && (i_icell_mask <= 0 || mask_of(i_cell) == mask_value);             // cell_is_valid, :1203-1215
+  if (!valid) { set_boundary(i_cell); return; }
+  for (int i = 0; i < ndim; ++i) YF(i, 1) = field[i];
+  int i_cell_prev = i_cell, status = 0, n_its = 0;
+  for (long iteration = 1;; ++iteration) {
+    if (status != 0) {                                                                           // :1081-1097
+      last_rejected = (int)std::min<long>(iteration - 1, 2000000000L);
+      dx = (1 - eps) * norm2(V3{r_p.x - r0[0], r_p.y - r0[1], r_p.z - r0[2]});
+      if (dx < min_dx) { set_boundary(i_cell); return; }
+    }
+    i_cell = i_cell_prev;
+    for (int i = 0; i < ndim; ++i) r0[i] = Y(i, n_steps);
+    for (int i = 0; i < nt; ++i) ys[i] = Y(i, n_steps);
+    for (int i = 0; i < ndim; ++i) field[i] = YF(i, n_steps);
+    unitvec(field, k[0]);
+    sub_int_builtin(integrand, ndim, nvar, field, k[0] + ndim);
+    auto substep = [&](int stage) -> bool {      // position ys -> r, walk, interpolate; false => cycle
+      for (int i = 0; i < ndim; ++i) r[i] = ys[i];
+      if (axisymmetric) r[0] = std::max(r[0], min_radius);
+      walk(g, std::numeric_limits<int>::max() - 1, {r0[0], r0[1], r0[2]}, {r[0], r[1], r[2]}, i_cell_prev, i_cell, r_p,
+           n_its, status, i_icell_mask, nullptr);
+      if (status != 0) return false;
+      interpolate_at_icell(g, r, ndim, i_field, field, i_cell);
+      unitvec(field, k[stage]);
+      sub_int_builtin(integrand, ndim, nvar, field, k[stage] + ndim);
+      return true;
+    };
+    { const double f = 0.5 * dx; for (int i = 0; i < nt; ++i) ys[i] = Y(i, n_steps) + f * k[0][i]; }      // :1118
+    if (!substep(1)) continue;
+    { const double f = 0.75 * dx; for (int i = 0; i < nt; ++i) ys[i] = Y(i, n_steps) + f * k[1][i]; }     // :1131
+    if (!substep(2)) continue;
+    { const double f = dx * inv_9;                                                                        // :1144-1145
+      for (int i = 0; i < nt; ++i) ys[i] = Y(i, n_steps) + f * ((2 * k[0][i] + 3 * k[1][i]) + 4 * k[2][i]); }
+    if (!substep(3)) continue;
+    { const double f = dx * inv_24;                                                                       // :1159-1160
+      for (int i = 0; i < nt; ++i) y_2nd[i] = Y(i, n_steps) + f * (((7 * k[0][i] + 6 * k[1][i]) + 8 * k[2][i]) + 3 * k[3][i]); }
+    double sum = 0;
+    for (int i = 0; i < nt; ++i) {
+      scales[i] = atol + std::max(std::fabs(ys[i]), std::fabs(y_2nd[i])) * rtol;
+      const double e = (ys[i] - y_2nd[i]) / scales[i];
+      sum += e * e;
+    }
+    const double err = std::sqrt(sum / 3);
+    if (err <= 1 || dx < 2 * min_dx) {                                                                    // :1165-1176
+      n_steps = n_steps + 1;
+      if (n_steps > max_steps) return;
+      for (int i = 0; i < nt; ++i) Y(i, n_steps) = ys[i];
+      if (axisymmetric) Y(0, n_steps) = std::max(Y(0, n_steps), min_radius);
+      for (int i = 0; i < ndim; ++i) YF(i, n_steps) = field[i];
+      i_cell_prev = i_cell;
+    } else {
+      last_rejected = (int)std::min<long>(iteration, 2000000000L);
+    }
+    const double max_growth = last_rejected > iteration - 2 ? 1.0 : 2.0;                                  // :1178-1184
+    const double dx_factor = std::min(max_growth, safety_fac * std::pow(1 / err, 1 / 3.0));
+    dx = std::max(min_dx, std::min(max_dx, dx * dx_factor));
+  }
+}
+
 // ---------------------------------------------------------------------------------
 // BINDA reader, m_binda.f90:52-194 (format written by convert_to_binary.py:68-115)
 // ---------------------------------------------------------------------------------
@@ -777,6 +878,23 @@ void iu_oracle_walk(void* h, int64_t n, int max_steps, const double* r0, const d
 void iu_oracle_point_is_inside_cell(void* h, int64_t n, const double* r, const int* i_cell, int* inside) {
   const Grid& g = *(Grid*)h;
   for (int64_t i = 0; i < n; ++i) inside[i] = (i_cell[i] >= 1 && point_is_inside_cell(g, r + 3 * i, i_cell[i])) ? 1 : 0;
+}
+
+// batched iu_integrate_along_field (built-in integrands, see integrate_along_field above).
+// y: (ndim+nvar, max_steps, n) inout, y_field: (ndim, max_steps, n) inout, n_steps[n] out,
+// boundary_material[n] inout or null.
+void iu_oracle_integrate_along_field(void* h, int64_t n, int ndim, int nvar, int integrand, const int* i_field, double min_dx,
+                                     double max_dx, int max_steps, double rtol, double atol, int reverse, double* y,
+                                     double* y_field, int* n_steps, int axisymmetric, int i_icell_mask, int mask_value,
+                                     int* boundary_material, int nn_mode, int nthreads) {
+  const Grid& g = *(Grid*)h;
+  const size_t ny = (size_t)(ndim + nvar) * max_steps, nf = (size_t)ndim * max_steps;
+  int nt = eff_threads(nthreads); (void)nt;
+#pragma omp parallel for num_threads(nt) schedule(dynamic, 64)
+  for (int64_t i = 0; i < n; ++i)
+    integrate_along_field(g, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, rtol, atol, reverse != 0, y + ny * i,
+                          y_field + nf * i, n_steps[i], axisymmetric != 0, i_icell_mask, mask_value,
+                          boundary_material ? boundary_material + i : nullptr, nn_mode);
 }
 
 int iu_oracle_max_threads() {

@@ -52,6 +52,9 @@ def lib():
         L.iu_oracle_get_icell_scalar_at.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_ip, C.c_int]
         L.iu_oracle_walk.argtypes = [C.c_void_p, C.c_int64, C.c_int, c_dp, c_dp, c_ip, c_ip, c_dp, c_ip, c_ip, C.c_int]
         L.iu_oracle_point_is_inside_cell.argtypes = [C.c_void_p, C.c_int64, c_dp, c_ip, c_ip]
+        L.iu_oracle_integrate_along_field.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, c_ip, C.c_double, C.c_double,
+                                                      C.c_int, C.c_double, C.c_double, C.c_int, c_dp, c_dp, c_ip, C.c_int, C.c_int,
+                                                      C.c_int, c_ip, C.c_int, C.c_int]
         L.iu_oracle_benchmark_pass.restype = C.c_double
         L.iu_oracle_benchmark_pass.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_dp, c_ip, C.c_int]
         _lib = L
@@ -243,6 +246,27 @@ class OracleGrid:
         st = np.zeros(n, dtype=np.int32)
         lib().iu_oracle_walk(self.h, n, int(max_steps), _d(r0), _d(r1), _i(ic0), _i(ic1), _d(r_p), _i(ns), _i(st), int(i_icell_mask))
         return ic1, r_p, ns, st
+
+    def integrate_along_field(self, y0, i_field, min_dx, max_dx, max_steps, rtol, atol, reverse=False, nvar=0, integrand=0,
+                              axisymmetric=False, i_icell_mask=0, mask_value=0, nn="brute", nthreads=0):
+        """Batched iu_integrate_along_field (:989-1217) with built-in integrands.  y0: (n, ndim+nvar)
+        initial position + state.  Returns y (n, max_steps, ndim+nvar), y_field (n, max_steps, ndim),
+        n_steps (n), boundary_material (n; -99 where the reference leaves it unset)."""
+        y0 = _f64(y0)
+        iv = _i32(i_field)
+        n, nt = y0.shape
+        ndim = len(iv)
+        assert nt == ndim + nvar
+        y = np.full((n, max_steps, nt), np.nan)
+        y[:, 0, :] = y0
+        yf = np.full((n, max_steps, ndim), np.nan)
+        ns = np.zeros(n, dtype=np.int32)
+        bm = np.full(n, -99, dtype=np.int32)
+        lib().iu_oracle_integrate_along_field(self.h, n, ndim, int(nvar), int(integrand), _i(iv), float(min_dx), float(max_dx),
+                                              int(max_steps), float(rtol), float(atol), int(bool(reverse)), _d(y), _d(yf), _i(ns),
+                                              int(bool(axisymmetric)), int(i_icell_mask), int(mask_value), _i(bm),
+                                              0 if nn == "kdtree2" else 1, nthreads)
+        return y, yf, ns, bm
 
     def point_is_inside_cell(self, r, i_cell):
         r = _f64(r)

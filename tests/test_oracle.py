@@ -138,3 +138,38 @@ def test_walk_outputs_status_and_mask():
     # max_steps exhausted: Fortran do-loop leaves n_steps = max_steps + 1
     ic1, r_p, ns, st = g.get_cell_through_neighbors(2, r0[:1], r1[:1], [1])
     assert ns[0] == 3 and st[0] == 0
+
+
+def _triangle_rotation_grid(golden_dir):
+    """test_trace_field.f90:16-23: triangle.binda plus point data vx = -y, vy = x."""
+    from interpolate_unstructured_b200 import binda
+    ent = {e.name: e.data for e in binda.read_binda(os.path.join(golden_dir, "triangle.binda")) if e.name != "point_data"}
+    pts = ent["points"].astype(np.float64)
+    pd = np.stack([-pts[:, 1], pts[:, 0]], axis=1)
+    return pts, ent["cells"], ent["cell_neighbors"], pd
+
+
+def test_trace_field_reference_criterion(golden_dir):
+    """test_trace_field.f90:25-53: tracing the rotation field from (1.5, 0) with the arc length
+    starting at -0.75 pi must reach the boundary within 100 steps (the only check the reference
+    makes); by construction the end point is about (0, 1.5) with length about 0 (comment at :43)."""
+    pts, cells, nb, pd = _triangle_rotation_grid(golden_dir)
+    o = OracleGrid.from_arrays("triangle", pts, cells, nb, pd)
+    y0 = np.array([[1.5, 0.0, -0.75 * np.pi]])
+    y, yf, ns, bm = o.integrate_along_field(y0, [1, 2], min_dx=1e-5, max_dx=1e-1, max_steps=100, rtol=1e-3, atol=1e-3,
+                                            nvar=1, integrand=1)
+    assert 1 < ns[0] <= 100                               # "Boundary not reached" otherwise (:50)
+    end = y[0, ns[0] - 1]
+    assert abs(end[0]) < 2e-2 and abs(end[1] - 1.5) < 2e-2 and abs(end[2]) < 2e-2
+    assert bm[0] == -1                                    # physical boundary
+    assert np.isnan(y[0, ns[0]:]).all()                   # later columns untouched
+    # stays on the circle of radius 1.5 within the tolerances, field = (-y, x) along the curve
+    rad = np.hypot(y[0, :ns[0], 0], y[0, :ns[0], 1])
+    assert np.abs(rad - 1.5).max() < 1e-2
+    assert np.abs(yf[0, :ns[0], 0] + y[0, :ns[0], 1]).max() < 1e-12
+    # reverse direction from the end comes back towards the start; a seed outside is reported at once
+    y2, _, ns2, bm2 = o.integrate_along_field(np.array([[5.0, 5.0, 0.0]]), [1, 2], 1e-5, 1e-1, 100, 1e-3, 1e-3, nvar=1, integrand=1)
+    assert ns2[0] == 1 and bm2[0] == -1
+    # max_steps too small: n_steps = max_steps + 1 and nothing written beyond the array (:1167-1168)
+    y3, _, ns3, _ = o.integrate_along_field(y0, [1, 2], 1e-5, 1e-1, 5, 1e-3, 1e-3, nvar=1, integrand=1)
+    assert ns3[0] == 6 and (y3[0, :5] == y[0, :5]).all()
