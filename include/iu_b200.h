@@ -181,6 +181,27 @@ int iu_b200_get_cell_through_neighbors_batch(iu_b200_grid* grid, int64_t n, int 
                                              const double* r1, const int32_t* ic0, int32_t* ic1, double* r_p,
                                              int32_t* n_steps, int32_t* status, int i_icell_mask);
 
+/* iu_integrate_along_field (:989-1217) for n field lines: adaptive Bogacki-Shampine RK3(2) along
+ * the vector field stored in point_data columns i_field[ndim] until a boundary is reached.
+ *   y        (ndim+nvar, max_steps, n) inout: y(:, 1, i) holds the start position and the initial
+ *            values of the nvar integrated variables; columns 2..n_steps(i) receive the curve;
+ *            later columns stay untouched
+ *   y_field  (ndim, max_steps, n) inout or NULL: the field along the curve
+ *   n_steps  number of points stored; max_steps + 1 if the boundary was not reached (:1167-1168)
+ *   i_icell_mask / mask_value: integrate only where icell_data(:, i_icell_mask) == mask_value
+ *            (i_icell_mask = 0: both optional arguments absent)
+ *   boundary_material (n) inout or NULL: -1 physical boundary, else the mask value of the cell
+ *            behind the material boundary; untouched for lines that ran out of steps
+ * The reference's callback sub_int (:61-74) cannot cross the C ABI per step on a GPU; `integrand`
+ * selects a built-in one: 0 none (nvar = 0), 1 dy_var(:) = 1 (arc length, test_trace_field.f90:57-64),
+ * 2 dy_var(:) = norm2(field).  ndim in 1..3, nvar in 0..3.  max_dx < min_dx and max_steps < 1 are
+ * errors as in the reference (:1036-1037). */
+int iu_b200_integrate_along_field_batch(iu_b200_grid* grid, int64_t n, int ndim, int nvar, int integrand,
+                                        const int32_t* i_field, double min_dx, double max_dx, int max_steps,
+                                        double rtol, double atol, int reverse, double* y, double* y_field,
+                                        int32_t* n_steps, int axisymmetric, int i_icell_mask, int mask_value,
+                                        int32_t* boundary_material);
+
 /* ---- the hot path, device buffers (no host<->device copies; asynchronous on `stream`) ------- */
 
 int iu_b200_find_nearby_cell_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int32_t* idx, void* stream);
@@ -199,6 +220,11 @@ int iu_b200_get_cell_through_neighbors_batch_dev(iu_b200_grid* grid, int64_t n, 
                                                  const double* r1, const int32_t* ic0, int32_t* ic1, double* r_p,
                                                  int32_t* n_steps, int32_t* status, int i_icell_mask,
                                                  void* stream);
+int iu_b200_integrate_along_field_batch_dev(iu_b200_grid* grid, int64_t n, int ndim, int nvar, int integrand,
+                                            const int32_t* i_field /* host */, double min_dx, double max_dx,
+                                            int max_steps, double rtol, double atol, int reverse, double* y,
+                                            double* y_field, int32_t* n_steps, int axisymmetric, int i_icell_mask,
+                                            int mask_value, int32_t* boundary_material, void* stream);
 /* The *_dev calls cannot return IU_B200_EHINT synchronously.  This call synchronises `stream`
  * and returns IU_B200_EHINT if any query since the last check carried i_cell > n_cells. */
 int iu_b200_check_dev(iu_b200_grid* grid, void* stream);

@@ -95,6 +95,10 @@ _SIGNATURES = {
     "iu_b200_get_cell_scalar_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp, c_vp]),
     "iu_b200_get_icell_scalar_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp, c_vp]),
     "iu_b200_get_cell_through_neighbors_batch_dev": (C.c_int, [c_vp, C.c_int64, C.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int, c_vp]),
+    "iu_b200_integrate_along_field_batch": (C.c_int, [c_vp, C.c_int64, C.c_int, C.c_int, C.c_int, c_ip, C.c_double, C.c_double, C.c_int,
+                                                    C.c_double, C.c_double, C.c_int, c_vp, c_vp, c_vp, C.c_int, C.c_int, C.c_int, c_vp]),
+    "iu_b200_integrate_along_field_batch_dev": (C.c_int, [c_vp, C.c_int64, C.c_int, C.c_int, C.c_int, c_ip, C.c_double, C.c_double, C.c_int,
+                                                        C.c_double, C.c_double, C.c_int, c_vp, c_vp, c_vp, C.c_int, C.c_int, C.c_int, c_vp, c_vp]),
     "iu_b200_check_dev": (C.c_int, [c_vp, c_vp]),
     "iu_b200_build_cell_neighbors": (C.c_int, [C.c_int, C.c_int32, C.c_int32, c_dp, c_ip, c_ip]),
     "iu_b200_export_geometry": (C.c_int, [c_vp, c_dp, c_dp, c_dp, c_dp]),
@@ -451,6 +455,30 @@ class Grid:
         _check(lib().iu_b200_get_cell_through_neighbors_batch(self._h, n, int(min(max_steps, 2**31 - 2)), _p(r0), _p(r1), _p(ic0),
                                                               _p(ic1), _p(r_p), _p(n_steps), _p(status), int(i_icell_mask)))
         return ic1, r_p, n_steps, status
+
+    def iu_integrate_along_field(self, y, i_field, min_dx, max_dx, rtol, atol, reverse=False, nvar=0, integrand=0,
+                                 y_field=None, axisymmetric=False, i_icell_mask=0, mask_value=0, boundary_material=None):
+        """iu_integrate_along_field (:989-1217) for n field lines.  ``y`` is (n, max_steps, ndim+nvar)
+        (= Fortran y(ndim+nvar, max_steps, n)) with y[:, 0, :] the start positions and initial values,
+        updated in place; the sub_int callback is replaced by ``integrand`` (0 none, 1 dy = 1,
+        2 dy = |field|).  Returns (y, y_field, n_steps, boundary_material)."""
+        iv = np.ascontiguousarray(i_field, dtype=np.int32).reshape(-1)
+        ndim = len(iv)
+        if not isinstance(y, np.ndarray) or y.dtype != np.float64 or not y.flags.c_contiguous or y.ndim != 3 or y.shape[2] != ndim + nvar:
+            raise ValueError("y must be a C-contiguous float64 array of shape (n, max_steps, ndim + nvar)")
+        n, max_steps = y.shape[0], y.shape[1]
+        if y_field is None:
+            y_field = np.full((n, max_steps, ndim), np.nan)
+        _inout(y_field, np.float64, (n, max_steps, ndim), "y_field")
+        if boundary_material is None:
+            boundary_material = np.full(n, -99, dtype=np.int32)
+        _inout(boundary_material, np.int32, (n,), "boundary_material")
+        n_steps = np.zeros(n, dtype=np.int32)
+        _check(lib().iu_b200_integrate_along_field_batch(
+            self._h, n, ndim, int(nvar), int(integrand), iv.ctypes.data_as(c_ip), float(min_dx), float(max_dx), int(max_steps),
+            float(rtol), float(atol), int(bool(reverse)), _p(y), _p(y_field), _p(n_steps), int(bool(axisymmetric)),
+            int(i_icell_mask), int(mask_value), _p(boundary_material)))
+        return y, y_field, n_steps, boundary_material
 
     # ---- the hot path, device tensors (no copies, asynchronous on the current torch stream) ----
     def generate_queries_dev(self, r, first, seed, lo, hi):

@@ -94,6 +94,9 @@ struct iu_b200_grid {
   // sort workspace (device API and host pipeline share it: all compute is stream-ordered by the caller)
   DevBuf<uint32_t> keys, keys_alt, idx, idx_alt;
   DevBuf<char> sort_temp;
+  // tracer workspace: seeds (3, n), their field (ndim, n) and cells
+  DevBuf<double> tr_seed, tr_field;
+  DevBuf<int32_t> tr_cell;
   // host pipeline
   cudaStream_t s_in = nullptr, s_comp = nullptr, s_out = nullptr;
   Slot slot[N_SLOTS];
@@ -382,6 +385,7 @@ int iu_b200_grid_destroy(iu_b200_grid* g) {
       sl.i_a.release(); sl.i_b.release(); sl.i_c.release(); sl.i_d.release();
     }
     g->keys.release(); g->keys_alt.release(); g->idx.release(); g->idx_alt.release(); g->sort_temp.release();
+    g->tr_seed.release(); g->tr_field.release(); g->tr_cell.release();
     if (g->s_in) cudaStreamDestroy(g->s_in);
     if (g->s_comp) cudaStreamDestroy(g->s_comp);
     if (g->s_out) cudaStreamDestroy(g->s_out);
@@ -883,6 +887,106 @@ void* iu_b200_host_alloc(size_t bytes) {
 }
 void iu_b200_host_free(void* p) {
   if (p) cudaFreeHost(p);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// field-line tracer (iu_integrate_along_field)
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+int trace_args_ok(const iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field, double min_dx,
+                  double max_dx, int max_steps, const void* y, const void* n_steps, int mask) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  if (n < 0) { set_error("negative count"); return IU_B200_EINVAL; }
+  if (ndim < 1 || ndim > 3 || nvar < 0 || nvar > TRACE_MAX_NVAR || !i_field) { set_error("need ndim in 1..3, nvar in 0..3"); return IU_B200_EINVAL; }
+  if (integrand < 0 || integrand > 2 || (integrand == 0 && nvar != 0)) { set_error("unknown integrand (0 needs nvar = 0)"); return IU_B200_EINVAL; }
+  for (int k = 0; k < ndim; ++k)
+    if (i_field[k] < 1 || i_field[k] > g->dg.n_pd) { set_error("i_field: column outside 1..n_point_data"); return IU_B200_EINVAL; }
+  if (max_dx < min_dx) { set_error("max_dx < min_dx"); return IU_B200_EINVAL; }              // :1036
+  if (max_steps < 1) { set_error("max_steps < 1"); return IU_B200_EINVAL; }                  // :1037
+  if (mask < 0 || mask > g->dg.n_icd) { set_error("i_icell_mask outside 0..n_icell_data"); return IU_B200_EINVAL; }
+  if (n > 0 && (!y || !n_steps)) { set_error("null array"); return IU_B200_EINVAL; }
+  return IU_B200_OK;
+}
+
+// y, y_field, n_steps, boundary_material are device pointers
+void run_trace(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field, double min_dx, double max_dx,
+               int max_steps, double rtol, double atol, int reverse, double* y, double* y_field, int32_t* n_steps,
+               int axisymmetric, int i_icell_mask, int mask_value, int32_t* boundary_material, cudaStream_t s) {
+  g->tr_seed.ensure((size_t)3 * n);
+  g->tr_field.ensure((size_t)ndim * n);
+  g->tr_cell.ensure((size_t)n);
+  g->n_launches += launch_trace_seeds(n, ndim, ndim + nvar, max_steps, y, g->tr_seed.p, s);
+  CU(cudaMemsetAsync(g->tr_cell.p, 0, (size_t)n * 4, s));                                    // i_cell = 0: cold, :1051
+  run_query(g, make_args(g, QM_INTERP, n, g->tr_seed.p, ndim, i_field, 0, g->tr_cell.p, g->tr_field.p, nullptr), s);
+  TraceArgs a;
+  a.n = n; a.ndim = ndim; a.nvar = nvar; a.integrand = integrand;
+  for (int k = 0; k < ndim; ++k) a.ivars[k] = i_field[k] - 1;
+  a.min_dx = min_dx; a.max_dx = max_dx; a.rtol = rtol; a.atol = atol; a.max_steps = max_steps;
+  a.reverse = reverse != 0; a.axisymmetric = axisymmetric != 0;
+  a.mask_col = i_icell_mask - 1; a.mask_value = mask_value; a.max_walk_steps = (int)g->max_walk_steps;
+  a.y = y; a.y_field = y_field; a.n_steps = n_steps; a.boundary_material = boundary_material;
+  a.i_cell0 = g->tr_cell.p; a.field0 = g->tr_field.p;
+  g->n_launches += launch_trace(g->dg, a, s);
+  CU(cudaGetLastError());
+}
+
+}  // namespace
+
+extern "C" {
+
+int iu_b200_integrate_along_field_batch_dev(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field,
+                                            double min_dx, double max_dx, int max_steps, double rtol, double atol, int reverse,
+                                            double* y, double* y_field, int32_t* n_steps, int axisymmetric, int i_icell_mask,
+                                            int mask_value, int32_t* boundary_material, void* stream) {
+  int rc = trace_args_ok(g, n, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, y, n_steps, i_icell_mask);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    run_trace(g, n, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, rtol, atol, reverse, y, y_field, n_steps,
+              axisymmetric, i_icell_mask, mask_value, boundary_material, (cudaStream_t)stream);
+    return IU_B200_OK;
+  });
+}
+
+// Host buffers: field lines are processed in chunks whose curves fit a bounded device buffer;
+// y / y_field go up first because columns beyond n_steps must come back untouched.
+int iu_b200_integrate_along_field_batch(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field,
+                                        double min_dx, double max_dx, int max_steps, double rtol, double atol, int reverse,
+                                        double* y, double* y_field, int32_t* n_steps, int axisymmetric, int i_icell_mask,
+                                        int mask_value, int32_t* boundary_material) {
+  int rc = trace_args_ok(g, n, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, y, n_steps, i_icell_mask);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    const size_t ny = (size_t)(ndim + nvar) * max_steps, nf = (size_t)ndim * max_steps;
+    const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n, (int64_t)((size_t(1) << 28) / (ny * 8))));   // <= 256 MB of curves
+    DevBuf<double> d_y, d_f;
+    DevBuf<int32_t> d_ns, d_bm;
+    d_y.alloc(ny * chunk);
+    if (y_field) d_f.alloc(nf * chunk);
+    d_ns.alloc(chunk);
+    if (boundary_material) d_bm.alloc(chunk);
+    cudaStream_t s = g->s_comp;
+    for (int64_t off = 0; off < n; off += chunk) {
+      const int64_t m = std::min(chunk, n - off);
+      CU(cudaMemcpyAsync(d_y.p, y + ny * off, ny * m * 8, cudaMemcpyHostToDevice, s));
+      if (y_field) CU(cudaMemcpyAsync(d_f.p, y_field + nf * off, nf * m * 8, cudaMemcpyHostToDevice, s));
+      if (boundary_material) CU(cudaMemcpyAsync(d_bm.p, boundary_material + off, (size_t)m * 4, cudaMemcpyHostToDevice, s));
+      run_trace(g, m, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, rtol, atol, reverse, d_y.p, d_f.p, d_ns.p,
+                axisymmetric, i_icell_mask, mask_value, d_bm.p, s);
+      CU(cudaMemcpyAsync(y + ny * off, d_y.p, ny * m * 8, cudaMemcpyDeviceToHost, s));
+      if (y_field) CU(cudaMemcpyAsync(y_field + nf * off, d_f.p, nf * m * 8, cudaMemcpyDeviceToHost, s));
+      CU(cudaMemcpyAsync(n_steps + off, d_ns.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s));
+      if (boundary_material) CU(cudaMemcpyAsync(boundary_material + off, d_bm.p, (size_t)m * 4, cudaMemcpyDeviceToHost, s));
+      CU(cudaStreamSynchronize(s));
+    }
+    return IU_B200_OK;
+  });
 }
 
 }  // extern "C"

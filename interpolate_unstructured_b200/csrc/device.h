@@ -85,6 +85,26 @@ struct WalkArgs {
   bool mark_early = false;          // write n_steps = INT32_MIN for rays shorter than tiny_distance (host pipeline)
 };
 
+// iu_integrate_along_field for n field lines (kernels.cu: k_trace).  Seeds are located and their
+// field interpolated beforehand by a cold QM_INTERP pass (i_cell0, field0).
+constexpr int TRACE_MAX_NVAR = 3;
+struct TraceArgs {
+  int64_t n = 0;
+  int ndim = 0, nvar = 0, integrand = 0;
+  int ivars[3] = {0, 0, 0};         // 0-based point_data columns of the field components
+  double min_dx = 0, max_dx = 0, rtol = 0, atol = 0;
+  int max_steps = 0;
+  int reverse = 0, axisymmetric = 0;
+  int mask_col = -1, mask_value = 0; // 0-based icell_data column, -1 = absent
+  int max_walk_steps = 1 << 20;
+  double* y = nullptr;              // (ndim+nvar, max_steps, n)
+  double* y_field = nullptr;        // (ndim, max_steps, n) or null
+  int32_t* n_steps = nullptr;
+  int32_t* boundary_material = nullptr;   // or null
+  const int32_t* i_cell0 = nullptr;
+  const double* field0 = nullptr;   // (ndim, n)
+};
+
 // every launcher returns the number of kernels it launched (for IU_B200_STAT_KERNEL_LAUNCHES)
 int launch_cell_centers(const DeviceGrid& g, const double* points, const int32_t* cells, double* centers, cudaStream_t s);
 int launch_build_records(const DeviceGrid& g, const double* points, const int32_t* cells, const int32_t* neighbors,
@@ -102,6 +122,8 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int morton_end_bit(const DeviceGrid& g);
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s);
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s);
+int launch_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const double* y, double* r, cudaStream_t s);
+int launch_trace(const DeviceGrid& g, const TraceArgs& a, cudaStream_t s);
 int launch_generate_queries(int64_t n, int64_t first, uint64_t seed, const double lo[3], const double hi[3], double* r,
                             cudaStream_t s);
 int launch_merge_rows(int64_t n, int row_bytes, const int32_t* i_cell, const void* src, void* dst, cudaStream_t s);

@@ -780,6 +780,149 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_walk(const double* __restrict
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// iu_integrate_along_field (:989-1217): Bogacki-Shampine RK3(2) along the interpolated field, one
+// field line per thread, the reference's statements in the reference's order.  The user callback
+// sub_int (:61-74) is replaced by built-in integrands (0 none, 1 dy = 1, 2 dy = norm2(field)).
+// The seed's cell and field come from a cold QM_INTERP pass (iu_interpolate_at at :1054).
+// ------------------------------------------------------------------------------------------------
+__global__ void k_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const double* __restrict__ y, double* __restrict__ r) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double* Y = y + (size_t)i * nt * max_steps;
+  r[3 * i] = Y[0];
+  r[3 * i + 1] = ndim > 1 ? Y[1] : 0.0;
+  r[3 * i + 2] = ndim > 2 ? Y[2] : 0.0;     // "Set unused coordinates to zero", :1045-1047
+}
+
+template <int CT>
+__global__ void __launch_bounds__(128) k_trace(const double* __restrict__ rec, const int32_t* __restrict__ dev_of_orig,
+                                               const double* __restrict__ pd, int pd_stride, const int32_t* __restrict__ icd,
+                                               int n_cells, unsigned long long* counters, const TraceArgs a) {
+  constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
+  using L = RecLayout<PPC>;
+  constexpr int MAXT = 3 + TRACE_MAX_NVAR;
+  const double safety_fac = 0.8, inv_24 = 1 / 24.0, inv_9 = 1 / 9.0, min_radius = 1e-12, eps = 1e-8;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  const int ndim = a.ndim, nvar = a.nvar, nt = ndim + nvar;
+  double* Y = a.y + (size_t)i * nt * a.max_steps;
+  double* YF = a.y_field ? a.y_field + (size_t)i * ndim * a.max_steps : nullptr;
+  const int32_t* mask = a.mask_col >= 0 ? icd + (size_t)a.mask_col * n_cells : nullptr;
+
+  int n_steps = 1;
+  const int ic_orig = a.i_cell0[i];
+  const bool valid = ic_orig > 0 && (!mask || __ldg(mask + (ic_orig - 1)) == a.mask_value);      // cell_is_valid, :1203-1215
+  if (!valid) {                                                                                   // :1057-1070
+    if (a.boundary_material) a.boundary_material[i] = ic_orig <= 0 ? -1 : (mask ? __ldg(mask + (ic_orig - 1)) : 0);
+    a.n_steps[i] = n_steps;
+    return;
+  }
+  double yc[MAXT], ys[MAXT], y2[MAXT], k[4][MAXT], field[3], fprev[3];
+#pragma unroll
+  for (int c = 0; c < MAXT; ++c) { yc[c] = c < nt ? Y[c] : 0.0; ys[c] = 0; y2[c] = 0; k[0][c] = k[1][c] = k[2][c] = k[3][c] = 0; }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { fprev[c] = c < ndim ? a.field0[(size_t)i * ndim + c] : 0.0; field[c] = fprev[c]; }
+  if (YF) for (int c = 0; c < ndim; ++c) YF[c] = fprev[c];
+  int ic_prev = __ldg(dev_of_orig + ic_orig), ic = ic_prev, status = 0;
+  long long last_rejected = -100;
+  double dx = a.max_dx;
+  V3 r0{0, 0, 0}, r_p{0, 0, 0};
+
+  auto unitvec = [&](double* out) {                                                              // get_unitvec, :1192-1201
+    const double nrm = norm2_3(V3{field[0], field[1], field[2]});
+#pragma unroll
+    for (int c = 0; c < 3; ++c) if (c < ndim) { out[c] = field[c] / nrm; if (a.reverse) out[c] = -out[c]; }
+    double dv = 1.0;
+    if (a.integrand == 2) dv = nrm;
+    for (int c = 0; c < nvar; ++c) out[ndim + c] = dv;                                           // sub_int
+  };
+  // position ys -> r, walk from (r0, ic_prev), interpolate the field there; false => "cycle"
+  auto substep = [&](double* kout) -> bool {
+    V3 r{ys[0], ndim > 1 ? ys[1] : 0.0, ndim > 2 ? ys[2] : 0.0};
+    if (a.axisymmetric) r.x = fmax(r.x, min_radius);
+    int n_its = 0; bool early;
+    walk_ray<PPC>(rec, r0, r, ic_prev, a.max_walk_steps, mask, ic, r_p, n_its, status, early);
+    if (!early && n_its > a.max_walk_steps) { status = -1; ic = 0; atomicAdd(counters + CNT_WALK_LIMIT, 1ULL); }
+    if (status != 0) return false;
+    const double* R = rec + (size_t)(ic - 1) * L::STRIDE;                                         // iu_interpolate_at_icell
+    const int32_t* RI = reinterpret_cast<const int32_t*>(R);
+    V3 p[PPC];
+    ld3n<PPC>(R + L::PTS, p);
+    Weights<CT> W;
+    W.setup(p, __ldg(R + L::VOL), r);
+    for (int v = 0; v < ndim; ++v) {
+      double d[4];
+#pragma unroll
+      for (int q = 0; q < PPC; ++q) d[q] = __ldg(pd + (size_t)__ldg(RI + L::CEL_I + q) * pd_stride + a.ivars[v]);
+      field[v] = W.apply(d);
+    }
+    unitvec(kout);
+    return true;
+  };
+  auto boundary = [&]() {                                                                         // :1087-1093
+    if (!a.boundary_material) return;
+    int bm = -1;
+    if (ic > 0 && mask) bm = __ldg(mask + (__ldg(reinterpret_cast<const int32_t*>(rec + (size_t)(ic - 1) * L::STRIDE) + L::ORG_I) - 1));
+    a.boundary_material[i] = bm;
+  };
+
+  const long long iter_cap = 64LL * a.max_steps + 100000;   // the reference loops to huge(1)-1; every pass shrinks dx or advances
+  for (long long iteration = 1; iteration <= iter_cap; ++iteration) {
+    if (status != 0) {                                                                            // :1081-1097
+      last_rejected = iteration - 1;
+      dx = (1 - eps) * norm2_3(r_p - r0);
+      if (dx < a.min_dx) { boundary(); break; }
+    }
+    ic = ic_prev;
+    r0 = V3{yc[0], ndim > 1 ? yc[1] : 0.0, ndim > 2 ? yc[2] : 0.0};
+#pragma unroll
+    for (int c = 0; c < 3; ++c) field[c] = fprev[c];
+    unitvec(k[0]);
+    { const double f = 0.5 * dx;
+#pragma unroll
+      for (int c = 0; c < MAXT; ++c) if (c < nt) ys[c] = yc[c] + f * k[0][c]; }                    // :1118
+    if (!substep(k[1])) continue;
+    { const double f = 0.75 * dx;
+#pragma unroll
+      for (int c = 0; c < MAXT; ++c) if (c < nt) ys[c] = yc[c] + f * k[1][c]; }                    // :1131
+    if (!substep(k[2])) continue;
+    { const double f = dx * inv_9;
+#pragma unroll
+      for (int c = 0; c < MAXT; ++c) if (c < nt) ys[c] = yc[c] + f * ((2 * k[0][c] + 3 * k[1][c]) + 4 * k[2][c]); }   // :1144-1145
+    if (!substep(k[3])) continue;
+    double sum = 0;
+    { const double f = dx * inv_24;
+#pragma unroll
+      for (int c = 0; c < MAXT; ++c) if (c < nt) {
+        y2[c] = yc[c] + f * (((7 * k[0][c] + 6 * k[1][c]) + 8 * k[2][c]) + 3 * k[3][c]);         // :1159-1160
+        const double scale = a.atol + fmax(fabs(ys[c]), fabs(y2[c])) * a.rtol;
+        const double e = (ys[c] - y2[c]) / scale;
+        sum += e * e;
+      } }
+    const double err = sqrt(sum / 3);
+    if (err <= 1 || dx < 2 * a.min_dx) {                                                          // :1165-1176
+      n_steps = n_steps + 1;
+      if (n_steps > a.max_steps) break;
+#pragma unroll
+      for (int c = 0; c < MAXT; ++c) if (c < nt) yc[c] = ys[c];
+      if (a.axisymmetric) yc[0] = fmax(yc[0], min_radius);
+      for (int c = 0; c < nt; ++c) Y[(size_t)(n_steps - 1) * nt + c] = yc[c];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) fprev[c] = field[c];
+      if (YF) for (int c = 0; c < ndim; ++c) YF[(size_t)(n_steps - 1) * ndim + c] = field[c];
+      ic_prev = ic;
+    } else {
+      last_rejected = iteration;
+    }
+    const double max_growth = last_rejected > iteration - 2 ? 1.0 : 2.0;                          // :1178-1184
+    const double dx_factor = fmin(max_growth, safety_fac * pow(1 / err, 1 / 3.0));
+    dx = fmax(a.min_dx, fmin(a.max_dx, dx * dx_factor));
+    if (iteration == iter_cap) atomicAdd(counters + CNT_WALK_LIMIT, 1ULL);
+  }
+  a.n_steps[i] = n_steps;
+}
+
 int sm_count() {
   static int n_sm = 0;
   if (n_sm == 0) {
@@ -990,6 +1133,24 @@ int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, g.depth, s);
   else if (g.cell_type == IU_QUAD_CT) launch_query_ct<IU_QUAD_CT>(a.mode, P, g.depth, s);
   else launch_query_ct<IU_TETRA_CT>(a.mode, P, g.depth, s);
+  return 1;
+}
+
+int launch_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const double* y, double* r, cudaStream_t s) {
+  if (n == 0) return 0;
+  k_trace_seeds<<<blocks_for(n, 256), 256, 0, s>>>(n, ndim, nt, max_steps, y, r);
+  return 1;
+}
+
+int launch_trace(const DeviceGrid& g, const TraceArgs& a, cudaStream_t s) {
+  if (a.n == 0) return 0;
+  const int b = blocks_for(a.n, 128);
+  if (g.cell_type == IU_TRIANGLE_CT)
+    k_trace<IU_TRIANGLE_CT><<<b, 128, 0, s>>>(g.rec, g.dev_of_orig, g.pd, g.pd_stride, g.icd, g.n_cells, g.counters, a);
+  else if (g.cell_type == IU_QUAD_CT)
+    k_trace<IU_QUAD_CT><<<b, 128, 0, s>>>(g.rec, g.dev_of_orig, g.pd, g.pd_stride, g.icd, g.n_cells, g.counters, a);
+  else
+    k_trace<IU_TETRA_CT><<<b, 128, 0, s>>>(g.rec, g.dev_of_orig, g.pd, g.pd_stride, g.icd, g.n_cells, g.counters, a);
   return 1;
 }
 

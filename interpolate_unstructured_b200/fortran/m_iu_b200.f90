@@ -252,22 +252,23 @@ module m_iu_b200
        integer(c_int) :: rc
      end function c_walk_batch
 
-     function c_trace_field_batch(grid, n, ndim, r_start, i_field, max_steps, min_dx, max_dx, rtol, atol, &
-          reverse, nvar, y_init, integrand, i_icell_mask, axisymmetric, y, n_steps, boundary_material) &
+     function c_trace_field_batch(grid, n, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, rtol, atol, &
+          reverse, y, y_field, n_steps, axisymmetric, i_icell_mask, mask_value, boundary_material) &
           bind(C, name="iu_b200_integrate_along_field_batch") result(rc)
        import
        type(c_ptr), value :: grid
        integer(c_int64_t), value :: n
-       integer(c_int), value :: ndim
-       real(c_double), intent(in) :: r_start(ndim, *)
+       integer(c_int), value :: ndim, nvar, integrand
        integer(c_int32_t), intent(in) :: i_field(*)
+       real(c_double), value :: min_dx, max_dx
        integer(c_int), value :: max_steps
-       real(c_double), value :: min_dx, max_dx, rtol, atol
-       integer(c_int), value :: reverse, nvar
-       real(c_double), intent(in) :: y_init(*)
-       integer(c_int), value :: integrand, i_icell_mask, axisymmetric
+       real(c_double), value :: rtol, atol
+       integer(c_int), value :: reverse
        real(c_double), intent(inout) :: y(ndim + nvar, max_steps, *)
-       integer(c_int32_t), intent(inout) :: n_steps(*), boundary_material(*)
+       real(c_double), intent(inout) :: y_field(ndim, max_steps, *)
+       integer(c_int32_t), intent(inout) :: n_steps(*)
+       integer(c_int), value :: axisymmetric, i_icell_mask, mask_value
+       integer(c_int32_t), intent(inout) :: boundary_material(*)
        integer(c_int) :: rc
      end function c_trace_field_batch
   end interface
@@ -585,39 +586,49 @@ contains
          "iu_get_cell_through_neighbors")
   end subroutine iu_get_cell_through_neighbors_batch
 
-  !> iu_integrate_along_field (:989-1217) for n field lines with a built-in integrand instead of
-  !> the sub_int callback: integrand = 0 none (nvar = 0), 1 arc length (dy = 1, as
-  !> test_trace_field.f90:57-64), 2 field magnitude.
-  subroutine iu_integrate_along_field_batch(ug, n, ndim, r_start, i_field, max_steps, min_dx, max_dx, &
-       rtol, atol, reverse, nvar, y_init, integrand, y, n_steps, boundary_material, &
-       i_icell_mask, axisymmetric)
+  !> iu_integrate_along_field (:989-1217) for n field lines.  Same argument order as the reference
+  !> except that the callback sub_int is replaced by `integrand` (0 none with nvar = 0, 1 dy = 1 as
+  !> in test_trace_field.f90:57-64, 2 dy = norm2(field)) and every per-line argument gains a
+  !> trailing dimension n.
+  subroutine iu_integrate_along_field_batch(ug, n, ndim, nvar, integrand, i_field, &
+       min_dx, max_dx, max_steps, rtol, atol, reverse, y, y_field, &
+       n_steps, axisymmetric, i_icell_mask, mask_value, boundary_material)
     type(iu_grid_t), intent(in)   :: ug
     integer(int64), intent(in)    :: n
-    integer, intent(in)           :: ndim
-    real(dp), intent(in)          :: r_start(ndim, n)
+    integer, intent(in)           :: ndim, nvar, integrand
     integer, intent(in)           :: i_field(ndim)
+    real(dp), intent(in)          :: min_dx, max_dx
     integer, intent(in)           :: max_steps
-    real(dp), intent(in)          :: min_dx, max_dx, rtol, atol
+    real(dp), intent(in)          :: rtol, atol
     logical, intent(in)           :: reverse
-    integer, intent(in)           :: nvar
-    real(dp), intent(in)          :: y_init(max(nvar, 1))
-    integer, intent(in)           :: integrand
     real(dp), intent(inout)       :: y(ndim+nvar, max_steps, n)
-    integer, intent(inout)        :: n_steps(n)
-    integer, intent(inout)        :: boundary_material(n)
+    real(dp), intent(inout)       :: y_field(ndim, max_steps, n)
+    integer, intent(out)          :: n_steps(n)
+    logical, intent(in)           :: axisymmetric
     integer, intent(in), optional :: i_icell_mask
-    logical, intent(in), optional :: axisymmetric
-    integer(c_int) :: mask, axi, rev
+    integer, intent(in), optional :: mask_value
+    integer, intent(inout), optional :: boundary_material(n)
+    integer(c_int) :: mask, mval, axi, rev
+    integer, allocatable :: bm(:)
 
-    mask = 0; if (present(i_icell_mask)) mask = i_icell_mask
-    axi = 0
-    if (present(axisymmetric)) then
-       if (axisymmetric) axi = 1
+    if (present(i_icell_mask) .neqv. present(mask_value)) &
+         error stop "present(i_icell_mask) .neqv. present(mask_value)"     ! :1038-1039
+    mask = 0; mval = 0
+    if (present(i_icell_mask)) then
+       mask = i_icell_mask; mval = mask_value
     end if
+    axi = 0; if (axisymmetric) axi = 1
     rev = 0; if (reverse) rev = 1
-    call check(c_trace_field_batch(ug%handle, n, ndim, r_start, i_field, max_steps, min_dx, max_dx, &
-         rtol, atol, rev, nvar, y_init, integrand, mask, axi, y, n_steps, boundary_material), &
-         "iu_integrate_along_field")
+    if (present(boundary_material)) then
+       call check(c_trace_field_batch(ug%handle, n, ndim, nvar, integrand, i_field, min_dx, max_dx, &
+            max_steps, rtol, atol, rev, y, y_field, n_steps, axi, mask, mval, boundary_material), &
+            "iu_integrate_along_field")
+    else
+       allocate(bm(n))
+       call check(c_trace_field_batch(ug%handle, n, ndim, nvar, integrand, i_field, min_dx, max_dx, &
+            max_steps, rtol, atol, rev, y, y_field, n_steps, axi, mask, mval, bm), &
+            "iu_integrate_along_field")
+    end if
   end subroutine iu_integrate_along_field_batch
 
   ! ---- the reference's scalar entry points: batches of one --------------------------------
