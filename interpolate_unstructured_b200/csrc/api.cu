@@ -171,7 +171,7 @@ void collect_timings(iu_b200_grid* g) {
 }
 
 void free_device_grid(DeviceGrid& d) {
-  cudaFree(d.node); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
+  cudaFree(d.node); cudaFree(d.box); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
   cudaFree(d.orig_of_dev); cudaFree(d.pd); cudaFree(d.cd); cudaFree(d.icd); cudaFree(d.counters);
   d = DeviceGrid();
 }
@@ -288,6 +288,8 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       }
       CU(cudaMemcpy(d.node, nodes.data(), nodes.size() * sizeof(double2), cudaMemcpyHostToDevice));
     }
+    CU(cudaMalloc((void**)&d.box, std::max<size_t>(32, tree.box.size() * sizeof(float))));
+    if (!tree.box.empty()) CU(cudaMemcpy(d.box, tree.box.data(), tree.box.size() * sizeof(float), cudaMemcpyHostToDevice));
     CU(cudaMemcpyAsync(d.orig_of_dev, tree.orig_of_slot.data(), n_slots * 4, cudaMemcpyHostToDevice, s));
     g->n_launches += launch_build_records(d, d_points.p, d_cells.p, d_neigh.p, d_centers.p, s);
     CU(cudaStreamSynchronize(s));
@@ -313,7 +315,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 16 +
+    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 16 + tree.box.size() * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));

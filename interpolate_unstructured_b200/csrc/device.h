@@ -42,6 +42,7 @@ struct DeviceGrid {
   int depth = 0;                   // levels of internal nodes = level of the deepest leaf
   double2* node = nullptr;         // n_internal x {split value, bits(split dimension)}, heap order
   double* centers4 = nullptr;      // n_leaves*LEAF x {x, y, z, bits(original id)}; padding = +inf
+  float* box = nullptr;            // (n_internal + n_leaves) x 8 floats: tight box of the centres below each node
   // mesh
   double* rec = nullptr;           // n_leaves*LEAF records
   int32_t* dev_of_orig = nullptr;  // [n_cells + 1], index = 1-based original id -> 1-based device id

@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstring>
 #include <future>
+#include <limits>
 #include <thread>
 
 #include "internal.h"
@@ -271,6 +272,18 @@ inline int leaves_left(int l) {
   return std::min(1 << (d - 1), l - (1 << (d - 2)));
 }
 
+// nearest floats on either side of a double (outward rounding of the node boxes)
+inline float float_below(double x) {
+  float f = (float)x;
+  if ((double)f > x) f = std::nextafterf(f, -std::numeric_limits<float>::infinity());
+  return f;
+}
+inline float float_above(double x) {
+  float f = (float)x;
+  if ((double)f < x) f = std::nextafterf(f, std::numeric_limits<float>::infinity());
+  return f;
+}
+
 struct Builder {
   CRec* rec;
   KdTreeHost* out;
@@ -280,6 +293,13 @@ struct Builder {
     if (l == 1) {
       int block = node - n_internal;
       for (int64_t j = lo; j < hi; ++j) out->orig_of_slot[(size_t)block * LEAF + (j - lo)] = rec[j].id + 1;
+      float* b = out->box.data() + 8 * (size_t)node;
+      for (int k = 0; k < 3; ++k) {
+        double mn = rec[lo].c[k], mx = rec[lo].c[k];
+        for (int64_t j = lo + 1; j < hi; ++j) { mn = std::min(mn, rec[j].c[k]); mx = std::max(mx, rec[j].c[k]); }
+        b[k] = float_below(mn);
+        b[3 + k] = float_above(mx);
+      }
       return;
     }
     double mn[3], mx[3];
@@ -320,8 +340,15 @@ void build_kdtree(const double* centers, int32_t n_cells, KdTreeHost& out) {
     rec[i].c[0] = centers[3 * (size_t)i]; rec[i].c[1] = centers[3 * (size_t)i + 1]; rec[i].c[2] = centers[3 * (size_t)i + 2];
     rec[i].id = i; rec[i].pad = 0;
   }
+  out.box.assign(L > 0 ? 8 * (size_t)(2 * L - 1) : 0, 0.0f);
   Builder b{rec.data(), &out, L - 1};
   if (n_cells > 0) b.build(0, 0, n_cells, L, 0);
+  for (int i = L - 2; i >= 0; --i) {   // internal nodes: union of the children, bottom-up
+    const float* a = out.box.data() + 8 * (size_t)(2 * i + 1);
+    const float* c = out.box.data() + 8 * (size_t)(2 * i + 2);
+    float* o = out.box.data() + 8 * (size_t)i;
+    for (int k = 0; k < 3; ++k) { o[k] = std::min(a[k], c[k]); o[3 + k] = std::max(a[3 + k], c[3 + k]); }
+  }
 }
 
 }  // namespace iu

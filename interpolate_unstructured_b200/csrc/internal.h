@@ -46,6 +46,9 @@ struct KdTreeHost {
   std::vector<double> split;        // n_leaves - 1
   std::vector<uint8_t> sdim;        // n_leaves - 1
   std::vector<int32_t> orig_of_slot;  // n_leaves*LEAF, 1-based original cell id, 0 = padding
+  // tight bounding box of the centres below every node (internal nodes and leaves, heap order),
+  // 8 floats per node {lo x, y, z, hi x, y, z, 0, 0}, lo rounded down / hi rounded up to float
+  std::vector<float> box;           // 8 * (2 * n_leaves - 1)
 };
 // centers: (3, Nc) as iu_get_cell_center computes them (:264-269)
 void build_kdtree(const double* centers, int32_t n_cells, KdTreeHost& out);

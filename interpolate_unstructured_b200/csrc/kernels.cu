@@ -35,6 +35,9 @@ constexpr int MAX_SM_NODES = 2047;         // top 11 tree levels staged in share
 #ifndef IU_WALK_256
 #define IU_WALK_256 0   // 1: 32-byte loads in the walk too (6 instead of 12 per cell, but spills at 64 registers: slower)
 #endif
+#ifndef IU_NODE_BOX
+#define IU_NODE_BOX 1   // 1: test the far child's tight centre box before descending into it (nearest_center)
+#endif
 #ifndef IU_STREAM_HINTS
 #define IU_STREAM_HINTS 1
 #endif
@@ -336,6 +339,7 @@ __global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lo
 struct TreeView {
   const double2* node;   // {split value, bits(split dimension)} per internal node, heap order
   const double* centers4;
+  const float* box;      // 8 floats per node (internal and leaf): tight box of the centres below it
   int n_internal;
   int n_sm_nodes;
 };
@@ -383,6 +387,21 @@ __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx
   }
 }
 
+// Squared distance from q to the node's centre box, evaluated like the leaf scan evaluates a
+// centre: (ox^2 + oy^2) + oz^2 in fp64 without FMA.  Every centre c below the node has
+// lo_k <= c_k <= hi_k (floats rounded outward), so by monotonicity of IEEE subtraction,
+// multiplication and addition the result is <= the COMPUTED squared distance of each of them:
+// pruning with '>' keeps the fp64 minimum and all its ties.
+__device__ __forceinline__ double box_distance(const float* b, double qx, double qy, double qz) {
+  float lx, ly, lz, hx, hy, hz, p0, p1;
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(lx), "=f"(ly), "=f"(lz), "=f"(hx), "=f"(hy), "=f"(hz), "=f"(p0), "=f"(p1) : "l"(b));
+  const double ox = fmax(fmax((double)lx - qx, qx - (double)hx), 0.0);
+  const double oy = fmax(fmax((double)ly - qy, qy - (double)hy), 0.0);
+  const double oz = fmax(fmax((double)lz - qz, qz - (double)hz), 0.0);
+  return (ox * ox + oy * oy) + oz * oz;
+}
+
 __device__ __forceinline__ int nearest_center(const TreeView& t, const double* s_split, const uint8_t* s_dim, float* s_lb,
                                               double qx, double qy, double qz) {
   NNState st{__longlong_as_double(0x7ff0000000000000LL), 0x7fffffffffffffffLL, -1};
@@ -415,7 +434,11 @@ __device__ __forceinline__ int nearest_center(const TreeView& t, const double* s
       pending ^= 1u << l;
       if (!(lb[l * QUERY_THREADS] > bf)) {
         const int p1 = (node + 1) >> (lvl - (l + 1));   // 1-based heap index of the path node at level l+1
-        node = (p1 ^ 1) - 1;                            // its sibling = the far child at level l
+        const int far = (p1 ^ 1) - 1;                   // its sibling = the far child at level l
+#if IU_NODE_BOX
+        if (box_distance(t.box + 8 * (size_t)far, qx, qy, qz) > st.best) continue;
+#endif
+        node = far;
         lvl = l + 1;
         found = true;
         break;
@@ -1111,7 +1134,7 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   QueryKernelParams P;
-  P.tree = TreeView{g.node, g.centers4, g.n_internal, g.n_sm_nodes};
+  P.tree = TreeView{g.node, g.centers4, g.box, g.n_internal, g.n_sm_nodes};
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;

@@ -79,13 +79,21 @@ def metrics(tag, n_queries):
                   open(os.path.join(ROOT, "profiles", "traffic.json"), "w"))
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
     hdr, out, seen = None, [], 0
-    for r in csv.reader(io.StringIO(src)):
-        if r and r[0] == "Line No":
+    for line in src.splitlines():
+        # not csv.reader: source lines with inline asm carry unescaped quotes; split on the
+        # separator and re-join whatever the source column was broken into
+        if not line.startswith('"'):
+            continue
+        r = line.strip()[1:-1].split('","')
+        if r[0] == "Line No":
             hdr = r
             seen += 1
             continue
-        if hdr is None or seen > 1 or not r or not r[0].isdigit():
+        if hdr is None or seen > 1 or not r[0].isdigit():
             continue
+        extra = len(r) - len(hdr)
+        if extra > 0:
+            r = [r[0], '","'.join(r[1:2 + extra])] + r[2 + extra:]
         out.append((int(r[0]), r[1], int(r[6]), int(r[7]), int(r[8]), r[hdr.index("stall_long_sb")]))
     ts, ti = sum(o[2] for o in out) or 1, sum(o[3] for o in out) or 1
     with open(os.path.join(ROOT, "profiles", f"{tag}_k_query_hot_lines.txt"), "w") as f:
