@@ -49,7 +49,9 @@ extern "C" {
 #define IU_B200_CELL_WALK_LIMIT (-2)
 
 /* options for iu_b200_set_option */
-#define IU_B200_OPT_SORT_QUERIES 1  /* 0 never, 1 always, 2 auto (default): Morton-sort batches   */
+#define IU_B200_OPT_SORT_QUERIES 1  /* 0 never, 1 always, 2 auto (default): Morton-sort batches;
+                                       3 = the caller's queries are already in a spatially coherent
+                                       order (no sort, no permutation, ticket-tile scheduling) */
 #define IU_B200_OPT_MAX_WALK_STEPS 2 /* step cap used where the reference passes huge(1); default 2^20 */
 #define IU_B200_OPT_HOST_CHUNK 3    /* queries per H2D/compute/D2H pipeline chunk (host API)      */
 #define IU_B200_OPT_DEV_BATCH 4     /* max queries per internal device sub-batch (workspace bound) */

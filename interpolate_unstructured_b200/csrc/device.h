@@ -10,13 +10,14 @@ namespace iu {
 
 // Per-cell record, device order (= kd-tree leaf-slot order), in doubles:
 //   ppc = 4 (quad, tetra), 256 B: [0..11] face normals n1..n4, [12..23] vertices p1..p4,
-//       [24,25] 4 x int32 neighbours (1-based device ids, <= 0 passed through),
-//       [26,27] 4 x int32 vertex ids (0-based), [28] volume, [29] int32 original id (1-based) + pad
+//       [24,25] 4 x int32 vertex ids (0-based), [26] volume, [27] int32 original id (1-based) + pad
+//       (one aligned 32-byte sector = everything the interpolation needs besides the vertices),
+//       [28,29] 4 x int32 neighbours (1-based device ids, <= 0 passed through)
 //   ppc = 3 (triangle), 192 B: [0..8] normals, [9] area, [10..18] vertices, [19] pad,
 //       [20,21] int32 {nb1, nb2, nb3, original id}, [22,23] int32 {c1, c2, c3, pad}
 template <int PPC> struct RecLayout;
 template <> struct RecLayout<4> {
-  static constexpr int STRIDE = 32, NRM = 0, PTS = 12, NBR_I = 48, CEL_I = 52, VOL = 28, ORG_I = 58;
+  static constexpr int STRIDE = 32, NRM = 0, PTS = 12, CEL_I = 48, VOL = 26, ORG_I = 54, NBR_I = 56, TAIL = 24;
 };
 template <> struct RecLayout<3> {
   static constexpr int STRIDE = 24, NRM = 0, PTS = 10, NBR_I = 40, CEL_I = 44, VOL = 9, ORG_I = 43;
@@ -78,6 +79,7 @@ struct WalkArgs {
   const double* r0 = nullptr;
   const double* r1 = nullptr;
   const int32_t* ic0 = nullptr;
+  const uint32_t* perm = nullptr;   // processing order (Morton order of r0), or null
   int32_t* ic1 = nullptr;
   double* r_p = nullptr;
   int32_t* n_steps = nullptr;

@@ -28,7 +28,14 @@ constexpr int QUERY_THREADS = 256;
 #ifndef IU_QUERY_MIN_BLOCKS
 #define IU_QUERY_MIN_BLOCKS 4   // resident CTAs per SM the hot kernel is compiled for (64 registers per thread)
 #endif
-constexpr int MAX_SM_NODES = 2047;         // top 11 tree levels staged in shared memory
+#ifndef IU_SM_NODES
+#define IU_SM_NODES 0      // tree nodes (top levels) staged in shared memory; 0 (default, measured faster: 16.95 -> 15.99 ms)
+                           // = every level through L1 (ld.global.nc): one load path, no branch, more L1 for the records
+#endif
+constexpr int MAX_SM_NODES = IU_SM_NODES > 0 ? IU_SM_NODES : 1;
+#ifndef IU_SELP
+#define IU_SELP 1          // 1: branch-free selection of the query coordinate of a node's split dimension
+#endif
 
 // Query inputs and results are touched exactly once per launch: mark them evict-first (ld/st .cs)
 // so that they do not push the cell records of the current Morton window out of L2.
@@ -207,7 +214,7 @@ __global__ void k_build_records(int n_slots, const int32_t* __restrict__ orig_of
     RI[L::CEL_I + k] = pid[k];
   }
   RI[L::ORG_I] = o;
-  if (PPC == 4) { RI[L::ORG_I + 1] = 0; R[30] = 0.0; R[31] = 0.0; }
+  if (PPC == 4) { RI[L::ORG_I + 1] = 0; R[30] = 0.0; R[31] = 0.0; }   // [27] hi word, [30], [31]: padding
   else { R[19] = 0.0; RI[L::CEL_I + 3] = 0; }
   // leaf centre block entry; the centre is the array the tree was built from (bit-identical to
   // sum(cell_points)/ppc at :429)
@@ -360,6 +367,29 @@ struct TreeView {
 // bound of the COMPUTED squared distance of every centre behind the plane, and the float bound is
 // <= it, so pruning with '>' never drops the true fp64 minimum or a tie.  Returns the 0-based
 // device slot, -1 if none.
+// q[k] for k = 0, 1, 2 without a branch (the compiler otherwise emits a divergent branch around
+// the 64-bit moves in the innermost loop of the search)
+__device__ __forceinline__ double select3(double qx, double qy, double qz, int k) {
+#if IU_SELP
+  double r;
+  asm("{\n\t.reg .pred p0, p1;\n\tsetp.eq.s32 p0, %4, 0;\n\tsetp.eq.s32 p1, %4, 1;\n\t"
+      "selp.f64 %0, %2, %3, p1;\n\tselp.f64 %0, %1, %0, p0;\n\t}"
+      : "=&d"(r) : "d"(qx), "d"(qy), "d"(qz), "r"(k));
+  return r;
+#else
+  return k == 0 ? qx : (k == 1 ? qy : qz);
+#endif
+}
+
+__device__ __forceinline__ void fetch_node(const double2* __restrict__ nodes, int n_sm_nodes, const double* s_split,
+                                           const uint8_t* s_dim, int node, double& s, int& k) {
+#if IU_SM_NODES > 0
+  if (node < n_sm_nodes) { s = s_split[node]; k = s_dim[node]; return; }
+#endif
+  const double2 nd = __ldg(nodes + node);
+  s = nd.x; k = __double2loint(nd.y);
+}
+
 struct NNState {
   double best;
   long long besto;
@@ -411,9 +441,8 @@ __device__ __forceinline__ int nearest_center(const TreeView& t, const double* s
   // first descent: best = +inf, every level stays pending until the filter below
   while (node < t.n_internal) {
     double s; int k;
-    if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
-    else { const double2 nd = __ldg(t.node + node); s = nd.x; k = __double2loint(nd.y); }
-    const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
+    fetch_node(t.node, t.n_sm_nodes, s_split, s_dim, node, s, k);
+    const double qk = select3(qx, qy, qz, k);
     const double d = qk - s;
     lb[lvl * QUERY_THREADS] = __double2float_rd(d * d);
     node = 2 * node + 1 + (qk < s ? 0 : 1);
@@ -447,9 +476,8 @@ __device__ __forceinline__ int nearest_center(const TreeView& t, const double* s
     if (!found) break;
     while (node < t.n_internal) {
       double s; int k;
-      if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
-      else { const double2 nd = __ldg(t.node + node); s = nd.x; k = __double2loint(nd.y); }
-      const double qk = k == 0 ? qx : (k == 1 ? qy : qz);
+      fetch_node(t.node, t.n_sm_nodes, s_split, s_dim, node, s, k);
+      const double qk = select3(qx, qy, qz, k);
       const double d = qk - s;
       const double d2 = d * d;
       lb[lvl * QUERY_THREADS] = __double2float_rd(d2);
@@ -621,11 +649,6 @@ struct QueryKernelParams {
   int ivars[MAX_VARS];
 };
 
-__device__ __forceinline__ void load_node(const TreeView& t, const double* s_split, const uint8_t* s_dim, int node, double& s, int& k) {
-  if (node < t.n_sm_nodes) { s = s_split[node]; k = s_dim[node]; }
-  else { const double2 nd = __ldg(t.node + node); s = nd.x; k = __double2loint(nd.y); }
-}
-
 // Everything after the start cell is known: ray walk from the start cell's centre (iu_get_cell,
 // :429-432), then the mode's output.  `start` is a 1-based device id; for QM_INTERP_ICELL it is the
 // containing cell itself (no walk).
@@ -635,8 +658,8 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
   using L = RecLayout<PPC>;
   int ic = start;
   if (MODE != QM_INTERP_ICELL) {
-    const double* c4 = P.tree.centers4 + 4 * (size_t)(start - 1);
-    const V3 r0{__ldg(c4), __ldg(c4 + 1), __ldg(c4 + 2)};                             // :429
+    const D4 c4 = ld256(P.tree.centers4 + 4 * (size_t)(start - 1));
+    const V3 r0{c4.x, c4.y, c4.z};                                                    // :429
     V3 r_p; int n_steps = 0, status; bool early;
     walk_ray<PPC>(P.rec, r0, V3{qx, qy, qz}, start, P.max_steps, nullptr, ic, r_p, n_steps, status, early);
     if (!early && n_steps > P.max_steps) {
@@ -647,7 +670,20 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
   }
   const double* R = P.rec + (size_t)(ic - 1) * L::STRIDE;
   const int32_t* RI = reinterpret_cast<const int32_t*>(R);
-  const int orig = __ldg(RI + L::ORG_I);
+  int orig, pid[4];
+  double vol;
+  if constexpr (PPC == 4) {   // vertex ids, volume and original id share one 32-byte sector
+    const D4 tail = ld256(R + L::TAIL);
+    pid[0] = __double2loint(tail.x); pid[1] = __double2hiint(tail.x);
+    pid[2] = __double2loint(tail.y); pid[3] = __double2hiint(tail.y);
+    vol = tail.z;
+    orig = __double2loint(tail.w);
+  } else {
+    orig = __ldg(RI + L::ORG_I);
+    const int4 c = __ldg(reinterpret_cast<const int4*>(RI + L::CEL_I));
+    pid[0] = c.x; pid[1] = c.y; pid[2] = c.z; pid[3] = c.w;
+    vol = __ldg(R + L::VOL);
+  }
   if (MODE != QM_INTERP_ICELL) ST_STREAM(P.i_cell + i, orig);
   if (MODE == QM_CELL_F64) {
     ST_STREAM(P.out_f64 + i, __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));          // :447
@@ -655,14 +691,9 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
     ST_STREAM(P.out_i32 + i, __ldg(P.icd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));         // :461
   } else if (MODE == QM_INTERP || MODE == QM_INTERP_ICELL) {                           // :498-527
     V3 p[PPC];
-    int pid[4];
     if (PPC == 4) ld3x4(R + L::PTS, p); else ld3n<PPC>(R + L::PTS, p);
-    {
-      const int4 c = __ldg(reinterpret_cast<const int4*>(RI + L::CEL_I));
-      pid[0] = c.x; pid[1] = c.y; pid[2] = c.z; pid[3] = c.w;
-    }
     Weights<CT> W;
-    W.setup(p, __ldg(R + L::VOL), V3{qx, qy, qz});
+    W.setup(p, vol, V3{qx, qy, qz});
     double* out = P.out_f64 + (size_t)i * P.n_vars;
     if (NV > 0) {
       double res[NV > 0 ? NV : 1];
@@ -731,7 +762,7 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
   __shared__ double s_split[MAX_SM_NODES];
   __shared__ uint8_t s_dim[MAX_SM_NODES + 1];
   extern __shared__ float s_lb[];   // [tree depth][QUERY_THREADS] plane-distance lower bounds (nearest_center)
-  if (MODE != QM_INTERP_ICELL) {
+  if (MODE != QM_INTERP_ICELL && IU_SM_NODES > 0) {
     for (int i = threadIdx.x; i < P.tree.n_sm_nodes; i += blockDim.x) {
       const double2 nd = P.tree.node[i];
       s_split[i] = nd.x; s_dim[i] = (uint8_t)__double2loint(nd.y);
@@ -785,7 +816,8 @@ template <int PPC>
 __global__ void __launch_bounds__(QUERY_THREADS) k_walk(const double* __restrict__ rec, const int32_t* __restrict__ dev_of_orig,
                                                         const int32_t* __restrict__ orig_of_dev, const int32_t* __restrict__ mask,
                                                         int n_cells, unsigned long long* counters, WalkArgs a) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += (int64_t)gridDim.x * blockDim.x) {
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < a.n; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = a.perm ? (int64_t)LD_STREAM(a.perm + t) : t;
     const int h = a.ic0[i];
     if (h < 1 || h > n_cells) { atomicAdd(counters + CNT_HINT_ERROR, 1ULL); continue; }
     const V3 r0 = ld3(a.r0 + 3 * i), r1 = ld3(a.r1 + 3 * i);
@@ -985,7 +1017,7 @@ void launch_query_static(const QueryKernelParams& P, int depth, cudaStream_t s) 
 // sched: 0 static grid-stride, 1 ticket tiles (sorted batches)
 template <int CT, int MODE, int NV>
 void launch_query_inst(const QueryKernelParams& P, int depth, cudaStream_t s) {
-  if (P.ticket && P.perm && P.sched >= 1) launch_query_static<CT, MODE, NV, 1>(P, depth, s);
+  if (P.ticket && P.sched >= 1) launch_query_static<CT, MODE, NV, 1>(P, depth, s);
   else launch_query_static<CT, MODE, NV, 0>(P, depth, s);
 }
 
@@ -1134,7 +1166,7 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   QueryKernelParams P;
-  P.tree = TreeView{g.node, g.centers4, g.box, g.n_internal, g.n_sm_nodes};
+  P.tree = TreeView{g.node, g.centers4, g.box, g.n_internal, g.n_sm_nodes < MAX_SM_NODES ? g.n_sm_nodes : MAX_SM_NODES};
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
