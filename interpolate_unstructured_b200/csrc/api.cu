@@ -272,7 +272,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     CU(cudaMalloc((void**)&d.node, std::max<size_t>(1, d.n_internal) * sizeof(double2)));
     CU(cudaMalloc((void**)&d.orig_of_dev, n_slots * 4));
     CU(cudaMalloc((void**)&d.dev_of_orig, ((size_t)n_cells + 1) * 4));
-    CU(cudaMalloc((void**)&d.centers4, n_slots * 32));
+    CU(cudaMalloc((void**)&d.centers4, n_slots * 24));
     CU(cudaMalloc((void**)&d.rec, n_slots * rec_stride(ppc) * 8));
     CU(cudaMalloc((void**)&d.counters, CNT_N * sizeof(unsigned long long)));
     CU(cudaMemsetAsync(d.counters, 0, CNT_N * sizeof(unsigned long long), s));
@@ -315,7 +315,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 16 + tree.box.size() * sizeof(float) +
+    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 16 + tree.box.size() * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));

@@ -166,10 +166,10 @@ __global__ void k_build_records(int n_slots, const int32_t* __restrict__ orig_of
   if (s >= n_slots) return;
   const int o = orig_of_dev[s];
   double* R = rec + (size_t)s * L::STRIDE;
-  double* C4 = centers4 + 4 * (size_t)s;
+  double* C3 = centers4 + 24 * (size_t)(s / LEAF) + (s % LEAF);   // leaf block: x[8], y[8], z[8]
   if (o <= 0) {   // padding slot of the last leaf block: never the nearest, never visited
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
-    C4[0] = inf; C4[1] = inf; C4[2] = inf; C4[3] = 0.0;
+    C3[0] = inf; C3[LEAF] = inf; C3[2 * LEAF] = inf;
     for (int i = 0; i < L::STRIDE; ++i) R[i] = 0.0;
     return;
   }
@@ -218,8 +218,7 @@ __global__ void k_build_records(int n_slots, const int32_t* __restrict__ orig_of
   else { R[19] = 0.0; RI[L::CEL_I + 3] = 0; }
   // leaf centre block entry; the centre is the array the tree was built from (bit-identical to
   // sum(cell_points)/ppc at :429)
-  C4[0] = centers[3 * c]; C4[1] = centers[3 * c + 1]; C4[2] = centers[3 * c + 2];
-  C4[3] = __longlong_as_double((long long)o);
+  C3[0] = centers[3 * c]; C3[LEAF] = centers[3 * c + 1]; C3[2 * LEAF] = centers[3 * c + 2];
 }
 
 template <int PPC>
@@ -238,7 +237,7 @@ __global__ void k_export_geometry(int n_slots, const int32_t* __restrict__ orig_
     if (normals) normals[c * 3 * PPC + i] = R[L::NRM + i];
   }
   if (volume) volume[c] = R[L::VOL];
-  if (centers) for (int i = 0; i < 3; ++i) centers[3 * c + i] = centers4[4 * (size_t)s + i];
+  if (centers) for (int i = 0; i < 3; ++i) centers[3 * c + i] = centers4[24 * (size_t)(s / LEAF) + i * LEAF + (s % LEAF)];
 }
 
 // column-major host layout (n_points, n_cols) -> point-major device table
@@ -345,7 +344,8 @@ __global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lo
 // ------------------------------------------------------------------------------------------------
 struct TreeView {
   const double2* node;   // {split value, bits(split dimension)} per internal node, heap order
-  const double* centers4;
+  const double* centers4;   // leaf blocks of 24 doubles: x[8], y[8], z[8] (padding slots = +inf)
+  const int32_t* orig_of_dev;   // original id per slot: read only to break exact distance ties
   const float* box;      // 8 floats per node (internal and leaf): tight box of the centres below it
   int n_internal;
   int n_sm_nodes;
@@ -392,27 +392,27 @@ __device__ __forceinline__ void fetch_node(const double2* __restrict__ nodes, in
 
 struct NNState {
   double best;
-  long long besto;
   int besti;
 };
 
 __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx, double qy, double qz, NNState& st) {
-  // two batches of four slots (4 independent 32-byte loads in flight each)
+  // two batches of four slots: x, y, z of four centres = three independent 32-byte loads
   const int base = (node - t.n_internal) * LEAF;
-  const double* c = t.centers4 + 4 * (size_t)base;
+  const double* c = t.centers4 + 3 * (size_t)base;
 #pragma unroll
   for (int h = 0; h < LEAF; h += 4) {
-    D4 a[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) a[j] = ld256(c + 4 * (h + j));
+    const D4 X = ld256(c + h), Y = ld256(c + LEAF + h), Z = ld256(c + 2 * LEAF + h);
+    const double xs[4] = {X.x, X.y, X.z, X.w}, ys[4] = {Y.x, Y.y, Y.z, Y.w}, zs[4] = {Z.x, Z.y, Z.z, Z.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const double dx = a[j].x - qx, dy = a[j].y - qy, dz = a[j].z - qz;
+      const double dx = xs[j] - qx, dy = ys[j] - qy, dz = zs[j] - qz;
       const double sd = (dx * dx + dy * dy) + dz * dz;
-      const long long o = __double_as_longlong(a[j].w);
-      // padding slots hold +inf centres (sd = inf or NaN): never selected because besti < 0 only
-      // while best = +inf and 'sd < best' is false for them
-      if (sd < st.best || (sd == st.best && o < st.besto && o > 0)) { st.best = sd; st.besti = base + h + j; st.besto = o; }
+      if (sd < st.best) { st.best = sd; st.besti = base + h + j; }
+      else if (sd == st.best) {
+        // exact tie (rare): the lowest original cell id wins; padding slots (+inf centres, id 0) never do
+        const int o = __ldg(t.orig_of_dev + base + h + j);
+        if (o > 0 && (st.besti < 0 || o < __ldg(t.orig_of_dev + st.besti))) st.besti = base + h + j;
+      }
     }
   }
 }
@@ -434,7 +434,7 @@ __device__ __forceinline__ double box_distance(const float* b, double qx, double
 
 __device__ __forceinline__ int nearest_center(const TreeView& t, const double* s_split, const uint8_t* s_dim, float* s_lb,
                                               double qx, double qy, double qz) {
-  NNState st{__longlong_as_double(0x7ff0000000000000LL), 0x7fffffffffffffffLL, -1};
+  NNState st{__longlong_as_double(0x7ff0000000000000LL), -1};
   float* lb = s_lb + threadIdx.x;   // lb[l * QUERY_THREADS]
   uint32_t pending = 0;
   int node = 0, lvl = 0;
@@ -658,8 +658,8 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
   using L = RecLayout<PPC>;
   int ic = start;
   if (MODE != QM_INTERP_ICELL) {
-    const D4 c4 = ld256(P.tree.centers4 + 4 * (size_t)(start - 1));
-    const V3 r0{c4.x, c4.y, c4.z};                                                    // :429
+    const double* c3 = P.tree.centers4 + 24 * (size_t)((start - 1) / LEAF) + ((start - 1) % LEAF);
+    const V3 r0{__ldg(c3), __ldg(c3 + LEAF), __ldg(c3 + 2 * LEAF)};                   // :429
     V3 r_p; int n_steps = 0, status; bool early;
     walk_ray<PPC>(P.rec, r0, V3{qx, qy, qz}, start, P.max_steps, nullptr, ic, r_p, n_steps, status, early);
     if (!early && n_steps > P.max_steps) {
@@ -1166,7 +1166,7 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   QueryKernelParams P;
-  P.tree = TreeView{g.node, g.centers4, g.box, g.n_internal, g.n_sm_nodes < MAX_SM_NODES ? g.n_sm_nodes : MAX_SM_NODES};
+  P.tree = TreeView{g.node, g.centers4, g.orig_of_dev, g.box, g.n_internal, g.n_sm_nodes < MAX_SM_NODES ? g.n_sm_nodes : MAX_SM_NODES};
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
