@@ -24,7 +24,10 @@ namespace {
 
 constexpr double TINY_DISTANCE = 1e-100;   // m_interp_unstructured.f90:20
 constexpr double HUGE_DISTANCE = 1e100;    // :738
-constexpr int QUERY_THREADS = 256;
+#ifndef IU_QUERY_THREADS
+#define IU_QUERY_THREADS 256
+#endif
+constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #ifndef IU_QUERY_MIN_BLOCKS
 #define IU_QUERY_MIN_BLOCKS 4   // resident CTAs per SM the hot kernel is compiled for (64 registers per thread)
 #endif
@@ -770,7 +773,10 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
     __syncthreads();
   }
   // SCHED = 1: warps draw STILE consecutive (sorted) queries at a time from the ticket counter
-  constexpr int STILE = 128;
+#ifndef IU_STILE
+#define IU_STILE 128
+#endif
+  constexpr int STILE = IU_STILE;
   const int lane = threadIdx.x & 31;
   int64_t t = SCHED ? 0 : (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t tile = 0;
