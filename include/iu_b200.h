@@ -121,6 +121,8 @@ int iu_b200_get_cell_data_index(const iu_b200_grid* grid, const char* name);
 int iu_b200_get_icell_data_index(const iu_b200_grid* grid, const char* name);
 /* name of a column (for iu_write_vtk-style consumers); NULL if out of range */
 const char* iu_b200_point_data_name(const iu_b200_grid* grid, int i_var);
+const char* iu_b200_cell_data_name(const iu_b200_grid* grid, int i_var);
+const char* iu_b200_icell_data_name(const iu_b200_grid* grid, int i_var);
 
 /* iu_add_point_data / iu_add_cell_data / iu_add_icell_data (:119-161): append a zero-filled
  * column called `name`; *i_var receives its 1-based index. */
@@ -244,6 +246,22 @@ int iu_b200_build_cell_neighbors(int cell_type, int32_t n_points, int32_t n_cell
  * Any pointer may be NULL. */
 int iu_b200_export_geometry(iu_b200_grid* grid, double* cell_points, double* cell_face_normals, double* cell_volume,
                             double* cell_centers);
+
+/* The raw mesh back from the device records, ORIGINAL order: points (3, Np), cells (ppc, Nc)
+ * 1-based.  Either pointer may be NULL.  Points no cell refers to come back as zeros. */
+int iu_b200_export_mesh(iu_b200_grid* grid, double* points, int32_t* cells);
+
+/* iu_write_vtk(ug, filename) (m_interp_unstructured.f90:930-985 through m_vtk.f90:45-221): the
+ * grid with its current cell, integer cell and point data as a .vtu file, byte for byte the
+ * reference's stream (XML header + appended raw blocks, Float32 points, 0-based connectivity).
+ * Columns without a name are called cell_data_<i> / icell_data_<i> / point_data_<i>. */
+int iu_b200_write_vtk(iu_b200_grid* grid, const char* filename);
+/* The same writer on host arrays (no device needed): points (3, Np), cells (ppc, Nc) 1-based,
+ * data tables column-major; name arrays may be NULL. */
+int iu_b200_write_vtk_arrays(const char* filename, int cell_type, int32_t n_points, int32_t n_cells, const double* points,
+                             const int32_t* cells, int n_cell_data, const double* cell_data, const char* const* cell_names,
+                             int n_icell_data, const int32_t* icell_data, const char* const* icell_names,
+                             int n_point_data, const double* point_data, const char* const* point_names);
 
 /* n query points uniform in [lo, hi] from a counter-based generator (SplitMix64 of
  * 3*(first+i)+k, seed), written to device memory r (3, n); used by the benchmark for the

@@ -68,6 +68,8 @@ _SIGNATURES = {
     "iu_b200_get_cell_data_index": (C.c_int, [c_vp, C.c_char_p]),
     "iu_b200_get_icell_data_index": (C.c_int, [c_vp, C.c_char_p]),
     "iu_b200_point_data_name": (C.c_char_p, [c_vp, C.c_int]),
+    "iu_b200_cell_data_name": (C.c_char_p, [c_vp, C.c_int]),
+    "iu_b200_icell_data_name": (C.c_char_p, [c_vp, C.c_int]),
     "iu_b200_add_point_data": (C.c_int, [c_vp, C.c_char_p, C.POINTER(C.c_int)]),
     "iu_b200_add_cell_data": (C.c_int, [c_vp, C.c_char_p, C.POINTER(C.c_int)]),
     "iu_b200_add_icell_data": (C.c_int, [c_vp, C.c_char_p, C.POINTER(C.c_int)]),
@@ -102,6 +104,10 @@ _SIGNATURES = {
     "iu_b200_check_dev": (C.c_int, [c_vp, c_vp]),
     "iu_b200_build_cell_neighbors": (C.c_int, [C.c_int, C.c_int32, C.c_int32, c_dp, c_ip, c_ip]),
     "iu_b200_export_geometry": (C.c_int, [c_vp, c_dp, c_dp, c_dp, c_dp]),
+    "iu_b200_export_mesh": (C.c_int, [c_vp, c_dp, c_ip]),
+    "iu_b200_write_vtk": (C.c_int, [c_vp, C.c_char_p]),
+    "iu_b200_write_vtk_arrays": (C.c_int, [C.c_char_p, C.c_int, C.c_int32, C.c_int32, c_dp, c_ip, C.c_int, c_dp, C.POINTER(C.c_char_p),
+                                         C.c_int, c_ip, C.POINTER(C.c_char_p), C.c_int, c_dp, C.POINTER(C.c_char_p)]),
     "iu_b200_generate_queries_dev": (C.c_int, [c_vp, C.c_int64, C.c_int64, C.c_uint64, c_dp, c_dp, c_vp, c_vp]),
     "iu_b200_host_alloc": (c_vp, [C.c_size_t]),
     "iu_b200_host_free": (None, [c_vp]),
@@ -198,6 +204,27 @@ def build_cell_neighbors(cells0, points, cell_type):
     _check(lib().iu_b200_build_cell_neighbors(ct, len(points), len(cells0), points.ctypes.data_as(c_dp),
                                               cells0.ctypes.data_as(c_ip), out.ctypes.data_as(c_ip)))
     return out
+
+
+def write_vtk_arrays(filename, cell_type, points, cells1, cell_data=None, icell_data=None, point_data=None):
+    """The library's VTU writer on host arrays (iu_write_vtk byte stream, m_vtk.f90:45-221); no GPU needed.
+    cells1 (Nc,ppc) 1-based; *_data = dict name -> column."""
+    ct = {"triangle": 1, "quad": 2, "tetra": 3}.get(cell_type, cell_type)
+    pts = np.ascontiguousarray(points, dtype=np.float64)
+    cl = np.ascontiguousarray(cells1, dtype=np.int32)
+
+    def pack(d, dt):
+        d = d or {}
+        names = (C.c_char_p * max(1, len(d)))(*[k.encode() for k in d])
+        a = np.ascontiguousarray(np.stack([np.asarray(v, dtype=dt) for v in d.values()]) if d else np.zeros((0,), dtype=dt))
+        return len(d), a, names
+
+    ncd, cd, cdn = pack(cell_data, np.float64)
+    nid, icd, icn = pack(icell_data, np.int32)
+    npd, pd, pdn = pack(point_data, np.float64)
+    _check(lib().iu_b200_write_vtk_arrays(os.fsencode(filename), ct, len(pts), len(cl), pts.ctypes.data_as(c_dp), cl.ctypes.data_as(c_ip),
+                                          ncd, cd.ctypes.data_as(c_dp), cdn, nid, icd.ctypes.data_as(c_ip), icn,
+                                          npd, pd.ctypes.data_as(c_dp), pdn))
 
 
 def _dev_ptr(t, dtype_name, n_elems, name):
@@ -367,6 +394,32 @@ class Grid:
         _check(lib().iu_b200_export_geometry(self._h, cp.ctypes.data_as(c_dp), fn.ctypes.data_as(c_dp),
                                              vol.ctypes.data_as(c_dp), ce.ctypes.data_as(c_dp)))
         return cp, fn, vol, ce
+
+    def _name(self, fn, i_var, prefix):
+        b = fn(self._h, int(i_var))
+        if b is None:
+            raise IndexError(i_var)
+        return b.decode() or f"{prefix}{i_var}"      # unnamed columns: the name iu_write_vtk gives them
+
+    def point_data_name(self, i_var):
+        return self._name(lib().iu_b200_point_data_name, i_var, "point_data_")
+
+    def cell_data_name(self, i_var):
+        return self._name(lib().iu_b200_cell_data_name, i_var, "cell_data_")
+
+    def icell_data_name(self, i_var):
+        return self._name(lib().iu_b200_icell_data_name, i_var, "icell_data_")
+
+    def export_mesh(self):
+        """points (Np,3) and cells (Nc,ppc) 1-based, rebuilt from the device records in original order."""
+        pts = np.empty((self.n_points, 3))
+        cells = np.empty((self.n_cells, self.n_points_per_cell), dtype=np.int32)
+        _check(lib().iu_b200_export_mesh(self._h, pts.ctypes.data_as(c_dp), cells.ctypes.data_as(c_ip)))
+        return pts, cells
+
+    def iu_write_vtk(self, filename):
+        """iu_write_vtk(ug, filename) (m_interp_unstructured.f90:930-985): the grid and its current data as .vtu."""
+        _check(lib().iu_b200_write_vtk(self._h, os.fsencode(filename)))
 
     # ---- the hot path, host arrays -----------------------------------------------------------
     def _prep(self, r, i_cell):

@@ -426,6 +426,14 @@ const char* iu_b200_point_data_name(const iu_b200_grid* g, int i_var) {
   if (!g || i_var < 1 || i_var > (int)g->point_names.size()) return nullptr;
   return g->point_names[i_var - 1].c_str();
 }
+const char* iu_b200_cell_data_name(const iu_b200_grid* g, int i_var) {
+  if (!g || i_var < 1 || i_var > (int)g->cell_names.size()) return nullptr;
+  return g->cell_names[i_var - 1].c_str();
+}
+const char* iu_b200_icell_data_name(const iu_b200_grid* g, int i_var) {
+  if (!g || i_var < 1 || i_var > (int)g->icell_names.size()) return nullptr;
+  return g->icell_names[i_var - 1].c_str();
+}
 
 }  // extern "C"
 
@@ -896,6 +904,67 @@ int iu_b200_export_geometry(iu_b200_grid* g, double* cell_points, double* cell_f
     if (cell_centers) CU(cudaMemcpy(cell_centers, ce.p, ce.n * 8, cudaMemcpyDeviceToHost));
     return IU_B200_OK;
   });
+}
+
+int iu_b200_export_mesh(iu_b200_grid* g, double* points, int32_t* cells) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    DeviceGuard guard(g->device);
+    DevBuf<double> p;
+    DevBuf<int32_t> c;
+    if (points) { p.alloc((size_t)3 * g->dg.n_points); CU(cudaMemset(p.p, 0, p.n * 8)); }
+    if (cells) c.alloc((size_t)g->dg.ppc * g->dg.n_cells);
+    CU(cudaDeviceSynchronize());
+    g->n_launches += launch_export_mesh(g->dg, p.p, c.p, nullptr);
+    CU(cudaDeviceSynchronize());
+    if (points) CU(cudaMemcpy(points, p.p, p.n * 8, cudaMemcpyDeviceToHost));
+    if (cells) CU(cudaMemcpy(cells, c.p, c.n * 4, cudaMemcpyDeviceToHost));
+    return IU_B200_OK;
+  });
+}
+
+int iu_b200_write_vtk(iu_b200_grid* g, const char* filename) {
+  if (!g || !filename) { set_error("null argument"); return IU_B200_EINVAL; }
+  const DeviceGrid& d = g->dg;
+  std::vector<double> points((size_t)3 * d.n_points), pd((size_t)d.n_points * d.n_pd), cd((size_t)d.n_cells * d.n_cd);
+  std::vector<int32_t> cells((size_t)d.ppc * d.n_cells), icd((size_t)d.n_cells * d.n_icd);
+  int rc = iu_b200_export_mesh(g, points.data(), cells.data());
+  if (rc == IU_B200_OK && d.n_pd > 0) rc = iu_b200_download_point_data(g, 1, d.n_pd, pd.data());
+  if (rc == IU_B200_OK && d.n_cd > 0) rc = iu_b200_download_cell_data(g, 1, d.n_cd, cd.data());
+  if (rc == IU_B200_OK && d.n_icd > 0) rc = iu_b200_download_icell_data(g, 1, d.n_icd, icd.data());
+  if (rc != IU_B200_OK) return rc;
+  auto named = [](const std::vector<std::string>& names, int n, const char* prefix, const void* data) {
+    VtuColumns c;
+    c.data = data;
+    for (int v = 0; v < n; ++v)   // columns created without a name (iu_b200_grid_create) get "<prefix><column>"
+      c.names.push_back(v < (int)names.size() && !names[v].empty() ? names[v] : prefix + std::to_string(v + 1));
+    return c;
+  };
+  if (!write_vtu(filename, d.cell_type, d.n_points, d.n_cells, points.data(), cells.data(),
+                 named(g->cell_names, d.n_cd, "cell_data_", cd.data()), named(g->icell_names, d.n_icd, "icell_data_", icd.data()),
+                 named(g->point_names, d.n_pd, "point_data_", pd.data())))
+    return IU_B200_EIO;
+  return IU_B200_OK;
+}
+
+int iu_b200_write_vtk_arrays(const char* filename, int cell_type, int32_t n_points, int32_t n_cells, const double* points,
+                             const int32_t* cells, int n_cell_data, const double* cell_data, const char* const* cell_names,
+                             int n_icell_data, const int32_t* icell_data, const char* const* icell_names,
+                             int n_point_data, const double* point_data, const char* const* point_names) {
+  if (!filename || !points || !cells || n_points < 0 || n_cells < 0 || cell_type < IU_TRIANGLE_CT || cell_type > IU_TETRA_CT) {
+    set_error("iu_b200_write_vtk_arrays: bad argument");
+    return IU_B200_EINVAL;
+  }
+  auto cols = [](int n, const void* data, const char* const* names, const char* prefix) {
+    VtuColumns c;
+    c.data = data;
+    for (int v = 0; v < n; ++v) c.names.push_back(names && names[v] && names[v][0] ? names[v] : prefix + std::to_string(v + 1));
+    return c;
+  };
+  return write_vtu(filename, cell_type, n_points, n_cells, points, cells, cols(n_cell_data, cell_data, cell_names, "cell_data_"),
+                   cols(n_icell_data, icell_data, icell_names, "icell_data_"), cols(n_point_data, point_data, point_names, "point_data_"))
+             ? IU_B200_OK : IU_B200_EIO;
 }
 
 int iu_b200_build_cell_neighbors(int cell_type, int32_t n_points, int32_t n_cells, const double* points,

@@ -114,6 +114,7 @@ int launch_build_records(const DeviceGrid& g, const double* points, const int32_
                          const double* centers, cudaStream_t s);
 int launch_export_geometry(const DeviceGrid& g, double* cell_points, double* normals, double* volume, double* centers,
                            cudaStream_t s);
+int launch_export_mesh(const DeviceGrid& g, double* points, int32_t* cells, cudaStream_t s);
 int launch_pack_point_data(const DeviceGrid& g, const double* cols, int col0, int n_cols, cudaStream_t s);
 int launch_unpack_point_data(const DeviceGrid& g, double* cols, int col0, int n_cols, cudaStream_t s);
 int launch_repack_point_data(const double* old_pd, int old_stride, double* new_pd, int new_stride, int n_cols,

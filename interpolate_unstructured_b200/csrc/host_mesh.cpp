@@ -255,6 +255,92 @@ bool build_cell_neighbors(int cell_type, int32_t n_points, int32_t n_cells, cons
 }
 
 // ------------------------------------------------------------------------------------------------
+// VTU writer
+// ------------------------------------------------------------------------------------------------
+bool write_vtu(const char* filename, int cell_type, int32_t n_points, int32_t n_cells, const double* points,
+               const int32_t* cells, const VtuColumns& cell_data, const VtuColumns& icell_data,
+               const VtuColumns& point_data) {
+  const int ppc = cell_type == IU_TRIANGLE_CT ? 3 : 4;
+  const int32_t vtk_type = cell_type == IU_TRIANGLE_CT ? 5 : (cell_type == IU_QUAD_CT ? 9 : 10);   // :941-950
+  FILE* f = std::fopen(filename, "wb");
+  if (!f) { set_error(std::string("cannot open ") + filename + " for writing"); return false; }
+  std::string xml;            // the header part (funit); the raw blocks (sunit) follow in `raw`
+  std::vector<char> raw;
+  int indent = 0;
+  long long offset = 0;
+  auto line = [&](const std::string& t) { xml.append((size_t)indent, ' '); xml += t; xml += '\n'; };
+  auto open_tag = [&](const char* name) { line(std::string("<") + name + ">"); indent += 2; };       // vtk_dat_xml
+  auto close_tag = [&](const char* name) { indent -= 2; line(std::string("</") + name + ">"); };
+  auto block = [&](const void* p, size_t bytes) {                                                    // "write(sunit) n_bytes, data"
+    const int32_t nb = (int32_t)bytes;
+    const char* h = reinterpret_cast<const char*>(&nb);
+    raw.insert(raw.end(), h, h + 4);
+    const char* d = reinterpret_cast<const char*>(p);
+    raw.insert(raw.end(), d, d + bytes);
+    offset += 4 + (long long)bytes;
+  };
+  xml += "<?xml version=\"1.0\"?>\n";                                                               // vtk_ini_xml
+  xml += "<VTKFile type=\"UnstructuredGrid\" version=\"0.1\" byte_order=\"LittleEndian\">\n";
+  indent = 2;
+  open_tag("UnstructuredGrid");
+  line("<Piece NumberOfPoints=\"" + std::to_string(n_points) + "\" NumberOfCells=\"" + std::to_string(n_cells) + "\">");
+  indent += 2;
+  open_tag("Points");                                                                               // vtk_unstr_geo_xml
+  line("<DataArray type=\"Float32\" NumberOfComponents=\"3\" Name=\"Points\" format=\"appended\" offset=\"" +
+       std::to_string(offset) + "\"/>");
+  {
+    std::vector<float> p32((size_t)3 * n_points);
+    for (size_t i = 0; i < p32.size(); ++i) p32[i] = (float)points[i];
+    block(p32.data(), p32.size() * 4);
+  }
+  close_tag("Points");
+  open_tag("Cells");                                                                                // vtk_unstr_con_xml
+  {
+    std::vector<int32_t> tmp((size_t)ppc * n_cells);
+    line("<DataArray type=\"Int32\" Name=\"connectivity\" format=\"appended\" offset=\"" + std::to_string(offset) + "\"/>");
+    for (size_t i = 0; i < tmp.size(); ++i) tmp[i] = cells[i] - 1;                                  // :957
+    block(tmp.data(), tmp.size() * 4);
+    line("<DataArray type=\"Int32\" Name=\"offsets\" format=\"appended\" offset=\"" + std::to_string(offset) + "\"/>");
+    tmp.resize((size_t)n_cells);
+    for (int32_t n = 0; n < n_cells; ++n) tmp[n] = (n + 1) * ppc;                                   // :952-954
+    block(tmp.data(), tmp.size() * 4);
+    line("<DataArray type=\"Int32\" Name=\"types\" format=\"appended\" offset=\"" + std::to_string(offset) + "\"/>");
+    for (int32_t n = 0; n < n_cells; ++n) tmp[n] = vtk_type;
+    block(tmp.data(), tmp.size() * 4);
+  }
+  close_tag("Cells");
+  auto columns = [&](const VtuColumns& c, size_t rows, bool is_int) {
+    for (size_t v = 0; v < c.names.size(); ++v) {
+      line(std::string("<DataArray type=\"") + (is_int ? "Int32" : "Float64") + "\" Name=\"" + c.names[v] +
+           "\" NumberOfComponents=\"1\" format=\"appended\" offset=\"" + std::to_string(offset) + "\"/>");
+      const size_t w = is_int ? 4 : 8;
+      block(reinterpret_cast<const char*>(c.data) + v * rows * w, rows * w);
+    }
+  };
+  open_tag("CellData");
+  columns(cell_data, (size_t)n_cells, false);
+  columns(icell_data, (size_t)n_cells, true);
+  close_tag("CellData");
+  open_tag("PointData");
+  columns(point_data, (size_t)n_points, false);
+  close_tag("PointData");
+  close_tag("Piece");                                                                               // vtk_unstr_geo_xml_close
+  close_tag("UnstructuredGrid");
+  line("<AppendedData encoding=\"raw\">");                                                          // vtk_end_xml
+  bool ok = std::fwrite(xml.data(), 1, xml.size(), f) == xml.size();
+  ok = ok && std::fputc('_', f) != EOF;
+  ok = ok && (raw.empty() || std::fwrite(raw.data(), 1, raw.size(), f) == raw.size());
+  xml.clear();
+  xml += '\n';
+  line("</AppendedData>");
+  close_tag("VTKFile");
+  ok = ok && std::fwrite(xml.data(), 1, xml.size(), f) == xml.size();
+  ok = (std::fclose(f) == 0) && ok;
+  if (!ok) set_error(std::string("short write to ") + filename);
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------------
 // kd-tree
 // ------------------------------------------------------------------------------------------------
 namespace {

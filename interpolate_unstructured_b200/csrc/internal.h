@@ -35,6 +35,17 @@ bool read_binda_mesh(const char* filename, double coord_scale_factor, HostMesh& 
 bool build_cell_neighbors(int cell_type, int32_t n_points, int32_t n_cells, const double* points,
                           const int32_t* cells, int32_t* neighbors);
 
+// ---- iu_write_vtk (m_interp_unstructured.f90:930-985 through m_vtk.f90:45-221) ------------------
+// Writes the same byte stream as the reference: XML header with appended raw data (int32 byte
+// count before each block), points as Float32, connectivity 0-based.  cells: (ppc, Nc) 1-based.
+struct VtuColumns {
+  std::vector<std::string> names;
+  const void* data = nullptr;   // column-major (n_rows, names.size()), double or int32
+};
+bool write_vtu(const char* filename, int cell_type, int32_t n_points, int32_t n_cells, const double* points,
+               const int32_t* cells, const VtuColumns& cell_data, const VtuColumns& icell_data,
+               const VtuColumns& point_data);
+
 // ---- nearest-centre kd-tree ------------------------------------------------------------------
 // Complete (left-balanced, heap-indexed) binary tree over the cell centres: n_leaves =
 // ceil(Nc / LEAF) leaf blocks of exactly LEAF slots (the last one padded), n_leaves - 1 internal

@@ -243,6 +243,26 @@ __global__ void k_export_geometry(int n_slots, const int32_t* __restrict__ orig_
   if (centers) for (int i = 0; i < 3; ++i) centers[3 * c + i] = centers4[24 * (size_t)(s / LEAF) + i * LEAF + (s % LEAF)];
 }
 
+// the raw mesh back from the records: cells(ppc, Nc) 1-based in original order, points(3, Np)
+// (every vertex of a cell carries its coordinates; vertices shared by several cells are written
+// several times with the same bits)
+template <int PPC>
+__global__ void k_export_mesh(int n_slots, const int32_t* __restrict__ orig_of_dev, const double* __restrict__ rec,
+                              double* points, int32_t* cells) {
+  using L = RecLayout<PPC>;
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_slots) return;
+  const int o = orig_of_dev[s];
+  if (o <= 0) return;
+  const double* R = rec + (size_t)s * L::STRIDE;
+  const int32_t* RI = reinterpret_cast<const int32_t*>(R);
+  for (int k = 0; k < PPC; ++k) {
+    const int pid = RI[L::CEL_I + k];
+    if (cells) cells[(size_t)(o - 1) * PPC + k] = pid + 1;
+    if (points) for (int d = 0; d < 3; ++d) points[3 * (size_t)pid + d] = R[L::PTS + 3 * k + d];
+  }
+}
+
 // column-major host layout (n_points, n_cols) -> point-major device table
 __global__ void k_pack_point_data(int n_points, int n_cols, int col0, int stride, const double* __restrict__ cols,
                                   double* __restrict__ pd) {
@@ -1093,6 +1113,15 @@ int launch_export_geometry(const DeviceGrid& g, double* cell_points, double* nor
   const int b = blocks_for(n_slots, 128);
   if (g.ppc == 3) k_export_geometry<3><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.rec, g.centers4, cell_points, normals, volume, centers);
   else k_export_geometry<4><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.rec, g.centers4, cell_points, normals, volume, centers);
+  return 1;
+}
+
+int launch_export_mesh(const DeviceGrid& g, double* points, int32_t* cells, cudaStream_t s) {
+  const int n_slots = g.n_leaves * LEAF;
+  if (n_slots == 0) return 0;
+  const int b = blocks_for(n_slots, 128);
+  if (g.ppc == 3) k_export_mesh<3><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.rec, points, cells);
+  else k_export_mesh<4><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.rec, points, cells);
   return 1;
 }
 

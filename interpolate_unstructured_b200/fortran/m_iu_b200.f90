@@ -71,6 +71,13 @@ module m_iu_b200
        integer(c_int) :: rc
      end function c_grid_destroy
 
+     function c_write_vtk(grid, filename) bind(C, name="iu_b200_write_vtk") result(rc)
+       import
+       type(c_ptr), value :: grid
+       character(kind=c_char), intent(in) :: filename(*)
+       integer(c_int) :: rc
+     end function c_write_vtk
+
      function c_grid_info(grid, info) bind(C, name="iu_b200_grid_info") result(rc)
        import
        type(c_ptr), value :: grid
@@ -306,6 +313,7 @@ module m_iu_b200
   public :: iu_sync_cell_data
   public :: iu_sync_icell_data
   public :: iu_destroy_grid
+  public :: iu_write_vtk
 
 contains
 
@@ -388,6 +396,14 @@ contains
     rc = c_grid_destroy(ug%handle)
     ug%handle = c_null_ptr
   end subroutine iu_destroy_grid
+
+  !> iu_write_vtk (:930-985): the device-resident grid with its current data as a .vtu file
+  !> (call iu_sync_*_data first if the host copies were modified)
+  subroutine iu_write_vtk(ug, filename)
+    type(iu_grid_t), intent(in)  :: ug
+    character(len=*), intent(in) :: filename
+    call check(c_write_vtk(ug%handle, c_string(trim(filename))), "iu_write_vtk")
+  end subroutine iu_write_vtk
 
   !> :106-116
   subroutine iu_get_point_data_index(ug, name, ix)
