@@ -179,6 +179,28 @@ def run_reference(args):
     print(json.dumps(out), flush=True)
 
 
+def bind_to_gpu_numa_node(local):
+    """Pin this rank (and therefore its first-touch pinned host buffers) to the CPUs of the NUMA node its GPU hangs
+    off: the host-buffer leg moves 64 B per query over PCIe and should not cross the socket interconnect."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return node
+    except (OSError, ValueError, AttributeError):
+        return None
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -191,6 +213,7 @@ def run_b200(args):
         raise SystemExit("bench.py needs a CUDA device: libiu_b200 has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa_node = bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -301,7 +324,8 @@ def run_b200(args):
         tt = max_over_ranks(tt)
         assert (ic_h >= 1).all() and np.abs(out_h[:, 0] - (r_h.sum(1) + 1)).max() < 1e-12
         e2e = {"value": world * ne * args.steps / tt, "unit": "queries/s", "h2d_bytes_per_step": ne * 28, "d2h_bytes_per_step": ne * (4 + 8 * N_VARS),
-               "queries_per_step": ne, "ms_per_step": tt / args.steps * 1e3, "host_memory": "pinned (iu_b200_host_alloc)"}
+               "queries_per_step": ne, "ms_per_step": tt / args.steps * 1e3, "host_memory": "pinned (iu_b200_host_alloc)",
+               "numa_node_rank0": numa_node}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
