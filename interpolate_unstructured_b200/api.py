@@ -585,6 +585,20 @@ class Grid:
             _dev_ptr(n_steps, "int32", n, "n_steps"), _dev_ptr(status, "int32", n, "status"), int(i_icell_mask),
             _cur_stream(self.device)))
 
+    def iu_integrate_along_field_dev(self, y, i_field, min_dx, max_dx, rtol, atol, n_steps, reverse=False, nvar=0, integrand=0,
+                                     y_field=None, axisymmetric=False, i_icell_mask=0, mask_value=0, boundary_material=None):
+        """iu_integrate_along_field on device tensors: y (n, max_steps, ndim+nvar) f64 with y[:, 0] set, n_steps (n) i32."""
+        iv = np.ascontiguousarray(i_field, dtype=np.int32).reshape(-1)
+        ndim = len(iv)
+        n, max_steps = y.shape[0], y.shape[1]
+        _check(lib().iu_b200_integrate_along_field_batch_dev(
+            self._h, n, ndim, int(nvar), int(integrand), iv.ctypes.data_as(c_ip), float(min_dx), float(max_dx), int(max_steps),
+            float(rtol), float(atol), int(bool(reverse)), _dev_ptr(y, "float64", n * max_steps * (ndim + nvar), "y"),
+            None if y_field is None else _dev_ptr(y_field, "float64", n * max_steps * ndim, "y_field"),
+            _dev_ptr(n_steps, "int32", n, "n_steps"), int(bool(axisymmetric)), int(i_icell_mask), int(mask_value),
+            None if boundary_material is None else _dev_ptr(boundary_material, "int32", n, "boundary_material"),
+            _cur_stream(self.device)))
+
     def check_dev(self):
         """Synchronises the current stream; raises IUError(E_HINT) if a ``*_dev`` call since the last
         check carried ``i_cell > n_cells`` (the reference's ``error stop`` at :490)."""

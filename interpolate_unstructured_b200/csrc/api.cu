@@ -1030,6 +1030,14 @@ void run_trace(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, co
   a.mask_col = i_icell_mask - 1; a.mask_value = mask_value; a.max_walk_steps = (int)g->max_walk_steps;
   a.y = y; a.y_field = y_field; a.n_steps = n_steps; a.boundary_material = boundary_material;
   a.i_cell0 = g->tr_cell.p; a.field0 = g->tr_field.p;
+  if (want_sort(g, QM_CELL, n) && n < (1LL << 31)) {   // lines in Morton order of their seeds
+    const int end_bit = morton_end_bit(g->dg);
+    g->keys.ensure(n); g->keys_alt.ensure(n); g->idx.ensure(n); g->idx_alt.ensure(n);
+    g->sort_temp.ensure(sort_temp_bytes(n, end_bit));
+    g->n_launches += launch_morton_sort(g->dg, n, g->tr_seed.p, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
+                                        g->sort_temp.p, g->sort_temp.n, nullptr, s);
+    a.perm = g->idx_alt.p;
+  }
   g->n_launches += launch_trace(g->dg, a, s);
   CU(cudaGetLastError());
 }

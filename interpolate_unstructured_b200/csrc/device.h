@@ -106,6 +106,7 @@ struct TraceArgs {
   int32_t* boundary_material = nullptr;   // or null
   const int32_t* i_cell0 = nullptr;
   const double* field0 = nullptr;   // (ndim, n)
+  const uint32_t* perm = nullptr;   // processing order (Morton order of the seeds), or null
 };
 
 // every launcher returns the number of kernels it launched (for IU_B200_STAT_KERNEL_LAUNCHES)

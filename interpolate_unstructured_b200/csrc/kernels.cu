@@ -884,8 +884,10 @@ __global__ void __launch_bounds__(128) k_trace(const double* __restrict__ rec, c
   using L = RecLayout<PPC>;
   constexpr int MAXT = 3 + TRACE_MAX_NVAR;
   const double safety_fac = 0.8, inv_24 = 1 / 24.0, inv_9 = 1 / 9.0, min_radius = 1e-12, eps = 1e-8;
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.n) return;
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= a.n) return;
+  // neighbouring threads trace neighbouring lines: their walks read the same records
+  const int64_t i = a.perm ? (int64_t)a.perm[t] : t;
   const int ndim = a.ndim, nvar = a.nvar, nt = ndim + nvar;
   double* Y = a.y + (size_t)i * nt * a.max_steps;
   double* YF = a.y_field ? a.y_field + (size_t)i * ndim * a.max_steps : nullptr;

@@ -175,12 +175,63 @@ def run_c5(a):
          {"setup_seconds": setup, "mesh_device_bytes": g.stats()["mesh_bytes"], "checks": {"located": nq, "linear_field_max_abs_err": err}})
 
 
+def run_trace(a):
+    """Batched field-line tracer (iu_integrate_along_field, test_trace_field style) on the C3 mesh: n lines from random
+    seeds through a swirl + drift field, arc-length integrand, host-buffer API (y crosses PCIe both ways)."""
+    n = 119
+    pts, cells = meshgen.kuhn_tet_mesh(n, jitter=0.10, seed=1234)
+    nb = api.build_cell_neighbors(cells, pts, "tetra")
+    c = pts - 0.5
+    field = np.stack([-c[:, 1] + 0.3 * c[:, 0], c[:, 0] + 0.3 * c[:, 1], 0.2 + 0.0 * c[:, 2]], axis=1)
+    g = api.Grid.from_arrays("tetra", pts, cells, nb, np.ascontiguousarray(field), device=0)
+    nl = int(a.queries or 5e5)
+    max_steps = 64
+    rng = np.random.default_rng(11)
+    seeds = rng.uniform(0.2, 0.8, size=(nl, 3))
+    h = 1.0 / n
+
+    def run():
+        y = np.full((nl, max_steps, 4), np.nan)
+        y[:, 0, :3] = seeds
+        y[:, 0, 3] = 0.0
+        t0 = time.perf_counter()
+        out = g.iu_integrate_along_field(y, [1, 2, 3], 1e-3 * h, 2.0 * h, 1e-4, 1e-6, nvar=1, integrand=1)
+        return time.perf_counter() - t0, out
+
+    run()
+    ts = []
+    for _ in range(max(1, a.steps)):
+        t, (y, yf, ns, bm) = run()
+        ts.append(t)
+    t = float(np.mean(ts))
+    steps = int(np.minimum(ns, max_steps).sum())
+    # the same lines with y resident in HBM (device API): seeds cold-located + k_trace
+    dev = torch.device("cuda", 0)
+    y_d = torch.full((nl, max_steps, 4), float("nan"), dtype=torch.float64, device=dev)
+    ns_d = torch.zeros(nl, dtype=torch.int32, device=dev)
+    seeds_d = torch.from_numpy(seeds).to(dev)
+
+    def run_dev():
+        y_d[:, 0, :3] = seeds_d
+        y_d[:, 0, 3] = 0.0
+        g.iu_integrate_along_field_dev(y_d, [1, 2, 3], 1e-3 * h, 2.0 * h, 1e-4, 1e-6, ns_d, nvar=1, integrand=1)
+
+    ms_dev = timed(run_dev, max(1, a.steps), 1)
+    g.check_dev()
+    assert torch.equal(ns_d.cpu(), torch.from_numpy(ns))
+    print(json.dumps({"workload": f"trace: {nl} field lines on the C3 mesh ({len(cells)} tets), RK3(2), max_steps {max_steps}, max_dx 2 h, rtol 1e-4, "
+                                  "arc-length integrand, host-buffer API", "lines": nl, "seconds": t, "lines_per_s": nl / t,
+                      "stored_steps": steps, "stored_steps_per_s": steps / t,
+                      "device_ms": ms_dev, "device_lines_per_s": nl / (ms_dev * 1e-3), "device_stored_steps_per_s": steps / (ms_dev * 1e-3), "mean_steps_per_line": steps / nl,
+                      "lines_that_left_the_domain": int((bm == -1).sum())}), flush=True)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("workload", choices=["C2", "C4", "C5"])
+    ap.add_argument("workload", choices=["C2", "C4", "C5", "trace"])
     ap.add_argument("--queries", type=float, default=0)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--mesh-n", type=int, default=0)
     a = ap.parse_args()
-    {"C2": run_c2, "C4": run_c4, "C5": run_c5}[a.workload](a)
+    {"C2": run_c2, "C4": run_c4, "C5": run_c5, "trace": run_trace}[a.workload](a)
