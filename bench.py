@@ -287,9 +287,11 @@ def run_b200(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, ncu_counters = None, None
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("k_query_dram_bytes_per_launch")
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get("k_query_dram_bytes_per_launch")
+        ncu_counters = dict(tj.get("counters") or {}, source="profiles/" + tj.get("source", ""))   # what actually limits k_query (ncu, last capture)
     except (OSError, ValueError):
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
@@ -297,7 +299,7 @@ def run_b200(args):
                 "algorithmic_bytes_per_launch": alg_bytes, "bytes_per_query": per_query, "mesh_raw_bytes": m_raw,
                 "peak_source": "MEASURED_PEAKS.json (measured)" if peaks else "fallback 6650 GB/s",
                 "kernel_share_of_step": st["query_kernel_ns"] * 1e-6 / (e0.elapsed_time(e1)),
-                "sort_share_of_step": st["sort_ns"] * 1e-6 / (e0.elapsed_time(e1))}
+                "sort_share_of_step": st["sort_ns"] * 1e-6 / (e0.elapsed_time(e1)), "ncu_counters": ncu_counters}
     gpu_launches = st["kernel_launches"] + args.steps      # + the i_cell memset kernel of each step
 
     # end to end through the host-buffer C ABI (pinned host memory; H2D + kernels + D2H per step)

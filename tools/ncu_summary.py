@@ -72,10 +72,15 @@ def metrics(tag, n_queries):
                 return float(row[i].replace(",", "")) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[units[i]]
             t = gb("dram__bytes_read.sum") + gb("dram__bytes_write.sum")
             traffic.append(t)
+            extra = {k: float(d[k].replace(",", "")) for k in ("l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct",
+                                                                 "l1tex__t_sector_hit_rate.pct", "smsp__thread_inst_executed_per_inst_executed.ratio",
+                                                                 "sm__warps_active.avg.pct_of_peak_sustained_active",
+                                                                 "dram__throughput.avg.pct_of_peak_sustained_elapsed") if k in d}
             if n_queries:
                 f.write(f"  -> DRAM traffic {t / 1e9:.2f} GB per launch = {t / n_queries:.0f} B/query at {n_queries} queries per launch\n")
     if traffic:
-        json.dump({"k_query_dram_bytes_per_launch": sum(traffic) / len(traffic), "queries_per_launch": n_queries, "source": f"{tag}_k_query.ncu-rep"},
+        json.dump({"k_query_dram_bytes_per_launch": sum(traffic) / len(traffic), "queries_per_launch": n_queries, "source": f"{tag}_k_query.ncu-rep",
+                   "counters": extra},
                   open(os.path.join(ROOT, "profiles", "traffic.json"), "w"))
     src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
     hdr, out, seen = None, [], 0
