@@ -419,9 +419,11 @@ struct NNState {
 };
 
 __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx, double qy, double qz, NNState& st) {
-  // two batches of four slots: x, y, z of four centres = three independent 32-byte loads
+  // two batches of four slots: x, y, z of four centres = three independent 32-byte loads.  The
+  // common path is branch-free (min / select); exact ties only raise a flag and are sorted out below.
   const int base = (node - t.n_internal) * LEAF;
   const double* c = t.centers4 + 3 * (size_t)base;
+  bool tie = false;
 #pragma unroll
   for (int h = 0; h < LEAF; h += 4) {
     const D4 X = ld256(c + h), Y = ld256(c + LEAF + h), Z = ld256(c + 2 * LEAF + h);
@@ -430,11 +432,20 @@ __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx
     for (int j = 0; j < 4; ++j) {
       const double dx = xs[j] - qx, dy = ys[j] - qy, dz = zs[j] - qz;
       const double sd = (dx * dx + dy * dy) + dz * dz;
-      if (sd < st.best) { st.best = sd; st.besti = base + h + j; }
-      else if (sd == st.best) {
-        // exact tie (rare): the lowest original cell id wins; padding slots (+inf centres, id 0) never do
-        const int o = __ldg(t.orig_of_dev + base + h + j);
-        if (o > 0 && (st.besti < 0 || o < __ldg(t.orig_of_dev + st.besti))) st.besti = base + h + j;
+      tie |= sd == st.best;
+      st.besti = sd < st.best ? base + h + j : st.besti;
+      st.best = sd < st.best ? sd : st.best;
+    }
+  }
+  if (tie) {
+    // some slot equalled the running minimum (rare): among all slots of this leaf at the final
+    // minimum and the incumbent, the lowest original cell id wins; padding slots (+inf, id 0) never do
+    for (int j = 0; j < LEAF; ++j) {
+      const double dx = __ldg(c + j) - qx, dy = __ldg(c + LEAF + j) - qy, dz = __ldg(c + 2 * LEAF + j) - qz;
+      const double sd = (dx * dx + dy * dy) + dz * dz;
+      if (sd == st.best && base + j != st.besti) {
+        const int o = __ldg(t.orig_of_dev + base + j);
+        if (o > 0 && (st.besti < 0 || o < __ldg(t.orig_of_dev + st.besti))) st.besti = base + j;
       }
     }
   }
@@ -475,7 +486,7 @@ __device__ __forceinline__ void nn_begin(const TreeView& t, const double* s_spli
     const double qk = select3(qx, qy, qz, k);
     const double d = qk - s;
     lb[lvl * QUERY_THREADS] = __double2float_rd(d * d);
-    node = 2 * node + 1 + (qk < s ? 0 : 1);
+    node = 2 * node + (qk < s ? 1 : 2);
     ++lvl;
   }
   scan_leaf(t, node, qx, qy, qz, L.st);
@@ -517,7 +528,7 @@ __device__ __forceinline__ bool nn_round(const TreeView& t, const double* s_spli
       const double d2 = d * d;
       lb[lvl * QUERY_THREADS] = __double2float_rd(d2);
       if (!(d2 > L.st.best)) pending |= 1u << lvl;
-      node = 2 * node + 1 + (qk < s ? 0 : 1);
+      node = 2 * node + (qk < s ? 1 : 2);
       ++lvl;
     }
     scan_leaf(t, node, qx, qy, qz, L.st);
