@@ -451,19 +451,21 @@ __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx
   }
 }
 
-// Squared distance from q to the node's centre box, evaluated like the leaf scan evaluates a
-// centre: (ox^2 + oy^2) + oz^2 in fp64 without FMA.  Every centre c below the node has
-// lo_k <= c_k <= hi_k (floats rounded outward), so by monotonicity of IEEE subtraction,
-// multiplication and addition the result is <= the COMPUTED squared distance of each of them:
-// pruning with '>' keeps the fp64 minimum and all its ties.
-__device__ __forceinline__ double box_distance(const float* b, double qx, double qy, double qz) {
+// Float LOWER bound of the squared distance from q to the node's centre box, with directed rounding
+// throughout: every centre c below the node has lo_k <= c_k <= hi_k (floats rounded outward), and
+// with qd <= q <= qu (q rounded down / up to float) the per-dimension offset
+// max(lo - qu, qd - hi, 0), each difference rounded down, is <= |c_k - q_k|; squares and sums are
+// rounded down too.  The caller prunes when the bound exceeds `best` rounded UP to float: two distinct
+// floats differ by 2^-24 relative, far more than the 2^-51 by which the fp64-computed distance of a
+// centre can fall below the exact one, so no centre at a distance <= best (ties included) is dropped.
+__device__ __forceinline__ float box_lower_bound(const float* b, double qx, double qy, double qz) {
   float lx, ly, lz, hx, hy, hz, p0, p1;
   asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=f"(lx), "=f"(ly), "=f"(lz), "=f"(hx), "=f"(hy), "=f"(hz), "=f"(p0), "=f"(p1) : "l"(b));
-  const double ox = fmax(fmax((double)lx - qx, qx - (double)hx), 0.0);
-  const double oy = fmax(fmax((double)ly - qy, qy - (double)hy), 0.0);
-  const double oz = fmax(fmax((double)lz - qz, qz - (double)hz), 0.0);
-  return (ox * ox + oy * oy) + oz * oz;
+  const float ox = fmaxf(fmaxf(__fsub_rd(lx, __double2float_ru(qx)), __fsub_rd(__double2float_rd(qx), hx)), 0.0f);
+  const float oy = fmaxf(fmaxf(__fsub_rd(ly, __double2float_ru(qy)), __fsub_rd(__double2float_rd(qy), hy)), 0.0f);
+  const float oz = fmaxf(fmaxf(__fsub_rd(lz, __double2float_ru(qz)), __fsub_rd(__double2float_rd(qz), hz)), 0.0f);
+  return __fadd_rd(__fadd_rd(__fmul_rd(ox, ox), __fmul_rd(oy, oy)), __fmul_rd(oz, oz));
 }
 
 // Search state of one query between rounds (nn_begin, then nn_round until it returns false).
@@ -511,7 +513,7 @@ __device__ __forceinline__ bool nn_round(const TreeView& t, const double* s_spli
       const int p1 = (node + 1) >> (lvl - (l + 1));   // 1-based heap index of the path node at level l+1
       const int far = (p1 ^ 1) - 1;                   // its sibling = the far child at level l
 #if IU_NODE_BOX
-      if (box_distance(t.box + 8 * (size_t)far, qx, qy, qz) > L.st.best) continue;
+      if (box_lower_bound(t.box + 8 * (size_t)far, qx, qy, qz) > bf) continue;
 #endif
       node = far;
       lvl = l + 1;
