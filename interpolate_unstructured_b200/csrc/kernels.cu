@@ -787,7 +787,11 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
           res[v] = W.apply(d);
         }
       }
-      if (NV % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+      if (NV % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 31) == 0) {   // one 32-byte streaming store per four values
+#pragma unroll
+        for (int v = 0; v < NV; v += 4)
+          asm volatile("st.global.cs.v4.f64 [%0], {%1,%2,%3,%4};" :: "l"(out + v), "d"(res[v]), "d"(res[v + 1]), "d"(res[v + 2]), "d"(res[v + 3]) : "memory");
+      } else if (NV % 2 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
 #pragma unroll
         for (int v = 0; v < NV; v += 2) ST_STREAM(reinterpret_cast<double2*>(out + v), make_double2(res[v], res[v + 1]));
       } else {
@@ -853,7 +857,19 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       if (t >= P.n) continue;
     } else if (t >= P.n) break;
     const int64_t i = P.perm ? (int64_t)LD_STREAM(P.perm + t) : t;
-    const double qx = LD_STREAM(P.r + 3 * i), qy = LD_STREAM(P.r + 3 * i + 1), qz = LD_STREAM(P.r + 3 * i + 2);
+    // a query's 24 bytes as two scattered loads instead of three: 16 + 8 or 8 + 16 bytes, whichever is aligned
+    double qx, qy, qz;
+    {
+      const double* rp = P.r + 3 * i;
+      if ((reinterpret_cast<uintptr_t>(rp) & 15) == 0) {
+        const double2 a = LD_STREAM(reinterpret_cast<const double2*>(rp));
+        qx = a.x; qy = a.y; qz = LD_STREAM(rp + 2);
+      } else {
+        qx = LD_STREAM(rp);
+        const double2 b = LD_STREAM(reinterpret_cast<const double2*>(rp + 1));
+        qy = b.x; qz = b.y;
+      }
+    }
     if (MODE == QM_NEAREST) {
       const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
       ST_STREAM(P.out_i32 + i, slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0);
