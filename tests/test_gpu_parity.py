@@ -368,3 +368,48 @@ def test_kernel_forms_agree_with_oracle(kind, n):
             assert (ic == oic).all() and (res == ores).all(), (form, nq)
             res, ic = g.iu_interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -7.5), i_cell=hint.copy())
             assert (ic == ohic).all() and (res == ohres).all(), (form, nq)
+
+
+# ---------------------------------------------------------------------------------------------
+# where the start cell matters: non-convex domains, queries outside, far away, NaN
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind,n", [("quad", 48), ("tetra", 10)])
+def test_nonconvex_domain_outside_and_nan_queries(kind, n):
+    """In a domain with a hole the ray from the nearest centre may leave the mesh (i_cell = 0) although
+    the query lies inside another cell (:427-432): the result then depends on the EXACT nearest centre,
+    so this pins the kd-tree search (boxes, float bounds, leaf blocks) against brute force far beyond
+    what convex meshes exercise.  Also: queries outside the bounding box, far away, and NaN."""
+    pts, cells, _ = _mesh(kind, n, seed=9)
+    if kind == "quad":
+        c = pts[cells].mean(1)
+        keep = ~((np.abs(c[:, 0] - 0.5) < 0.2) & (np.abs(c[:, 1] - 0.45) < 0.25)) & ~((c[:, 0] > 0.7) & (c[:, 1] > 0.7))
+    else:
+        c = pts[cells].mean(1)
+        keep = ~((np.abs(c - 0.5) < 0.22).all(1)) & ~((c[:, 0] > 0.75) & (c[:, 2] < 0.3))
+    cells = np.ascontiguousarray(cells[keep])
+    nb = api.build_cell_neighbors(cells, pts, kind)
+    pd = meshgen.smooth_fields(pts, 2)
+    g = api.Grid.from_arrays(kind, pts, cells, nb, pd)
+    o = OracleGrid.from_arrays(kind, pts, cells, nb, pd)
+    nq = 150_000
+    r = meshgen.uniform_queries(nq, [-0.3, -0.3, -0.3 if kind == "tetra" else 0.0], [1.3, 1.3, 1.3 if kind == "tetra" else 0.0], 77)
+    r[:50] *= 1e6                                                 # far away
+    r[50:60] = np.nan
+    r_oracle = r.copy()                                           # the reference (and the oracle) index out of bounds on an
+    r[60, 0] = np.inf                                             # infinite coordinate; the library reports "not found"
+    for sort in (0, 1):
+        g.set_option(api.OPT_SORT_QUERIES, sort)
+        sentinel = 7.5
+        res, ic = g.iu_interpolate_at(r, [1, 2], var_at_r=np.full((nq, 2), sentinel))
+        ores, oic = o.interpolate_at(r_oracle, [1, 2], var_at_r=np.full((nq, 2), sentinel), nn="brute")
+        finite = np.isfinite(r).all(1)
+        assert (ic[finite] == oic[finite]).all()
+        assert (res[finite] == ores[finite]).all()
+        assert (ic[~finite] < 1).all() and (res[~finite] == sentinel).all()
+        nn = g.find_nearby_cell_kdtree(r[finite])
+        onn, _, _ = o.nearest(r[finite], "brute")
+        assert (nn == onn).all()
+    inside_hole_or_out = (ic < 1) & finite
+    found = ic >= 1
+    assert inside_hole_or_out.sum() > nq // 10 and found.sum() > nq // 10
+    assert o.point_is_inside_cell(r[found], ic[found]).all()
