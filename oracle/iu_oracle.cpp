@@ -444,6 +444,9 @@ void get_cell(const Grid& g, const double* r, int& i_cell, int nn_mode, int* n_s
   int i_start;
   if (i_cell < 1) i_start = nn_mode == 0 ? find_nearby_cell_kdtree(g, r) : find_nearby_cell_brute(g, r, nullptr, nullptr);
   else i_start = i_cell;
+  // "Cell index is out of range" error stop of find_nearby_cell_kdtree (:282-286): reachable only when no
+  // centre has a comparable distance (infinite / NaN coordinates); reported as "not found" instead of aborting
+  if (i_start < 1 || i_start > g.n_cells) { i_cell = 0; if (n_steps_out) *n_steps_out = 0; return; }
   V3 r0 = cell_center(g, i_start);
   V3 r_p{0, 0, 0};
   int n_steps = 0, status = 0;
