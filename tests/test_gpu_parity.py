@@ -274,6 +274,26 @@ def test_walk_status_mask_early_and_step_cap():
     assert ns[0] == 3 and st[0] == 0                       # Fortran do-loop: max_steps + 1
 
 
+def test_walk_batch_sorted_and_unsorted_agree_with_oracle():
+    """iu_get_cell_through_neighbors on a batch, processed in input order and (IU_B200_OPT_SORT_QUERIES = 1) in Morton
+    order of the start positions: same bits, equal to the oracle, material mask included."""
+    g, o, pts = _both_from_mesh("tetra", 10, n_vars=1, cell_data=True)
+    n = 120_000
+    r0 = _queries(pts, n, 31)
+    ic0 = g.iu_get_cell(r0)
+    assert (ic0 >= 1).all()
+    rng = np.random.default_rng(3)
+    r1 = r0 + rng.normal(scale=0.08, size=(n, 3))                # several cells away, some leave the domain
+    exp = o.get_cell_through_neighbors(50, r0, r1, ic0, i_icell_mask=2)
+    for sort in (0, 1):
+        g.set_option(api.OPT_SORT_QUERIES, sort)
+        g.set_option(api.OPT_HOST_CHUNK, 50_000)
+        got = g.iu_get_cell_through_neighbors(50, r0, r1, ic0, i_icell_mask=2)
+        for a, b in zip(got, exp):
+            assert np.array_equal(a, b, equal_nan=True), sort
+    assert (exp[3] == -1).sum() > 10 and (exp[3] == 1).sum() > 100 and (exp[3] == 0).sum() > 100
+
+
 def test_error_behaviour():
     g, o, pts = _both_from_mesh("tetra", 4, n_vars=2)
     r = _queries(pts, 100, 1)

@@ -79,6 +79,17 @@ def test_trace_parity(kind, n, ndim, variant):
     gy, gf, gns, gbm = g.iu_integrate_along_field(y, i_field, 1e-4, 2e-2, 1e-4, 1e-6, **kw)
     oy, of, ons, obm = o.integrate_along_field(y0, i_field, 1e-4, 2e-2, max_steps, 1e-4, 1e-6, **kw)
     _compare(gy, gf, gns, gbm, oy, of, ons, obm, max_steps)
+    # lines traced in Morton order of their seeds (forced on for this small batch) give the same bits as in input order
+    g.set_option(api.OPT_SORT_QUERIES, 1)
+    y2 = np.full((nl, max_steps, ndim + nvar), np.nan)
+    y2[:, 0] = y0
+    sy, sf, sns, sbm = g.iu_integrate_along_field(y2, i_field, 1e-4, 2e-2, 1e-4, 1e-6, **kw)
+    g.set_option(api.OPT_SORT_QUERIES, 0)
+    y3 = np.full((nl, max_steps, ndim + nvar), np.nan)
+    y3[:, 0] = y0
+    uy, uf, uns, ubm = g.iu_integrate_along_field(y3, i_field, 1e-4, 2e-2, 1e-4, 1e-6, **kw)
+    assert np.array_equal(sy, uy, equal_nan=True) and np.array_equal(sf, uf, equal_nan=True)
+    assert np.array_equal(sns, uns) and np.array_equal(sbm, ubm) and np.array_equal(sy, gy, equal_nan=True)
     assert (gns == 1).sum() >= 20
     assert (gbm[:20] == -1).all()
     if variant == "magnitude_mask":
