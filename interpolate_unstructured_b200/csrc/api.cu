@@ -171,7 +171,7 @@ void collect_timings(iu_b200_grid* g) {
 }
 
 void free_device_grid(DeviceGrid& d) {
-  cudaFree(d.node); cudaFree(d.box); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
+  cudaFree(d.node); cudaFree(d.fat); cudaFree(d.box); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
   cudaFree(d.orig_of_dev); cudaFree(d.pd); cudaFree(d.cd); cudaFree(d.icd); cudaFree(d.counters);
   d = DeviceGrid();
 }
@@ -287,6 +287,19 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
         nodes[i] = make_double2(tree.split[i], bits);
       }
       CU(cudaMemcpy(d.node, nodes.data(), nodes.size() * sizeof(double2), cudaMemcpyHostToDevice));
+      // the same nodes with their children's splits alongside: {split, split(2i+1), split(2i+2), dimensions}
+      std::vector<double> fat((size_t)4 * d.n_internal, 0.0);
+      for (int i = 0; i < d.n_internal; ++i) {
+        unsigned long long dims = tree.sdim[i];
+        fat[4 * (size_t)i] = tree.split[i];
+        for (int c = 0; c < 2; ++c) {
+          const long long ch = 2LL * i + 1 + c;
+          if (ch < d.n_internal) { fat[4 * (size_t)i + 1 + c] = tree.split[ch]; dims |= (unsigned long long)tree.sdim[ch] << (2 + 2 * c); }
+        }
+        std::memcpy(&fat[4 * (size_t)i + 3], &dims, 8);
+      }
+      CU(cudaMalloc((void**)&d.fat, fat.size() * sizeof(double)));
+      CU(cudaMemcpy(d.fat, fat.data(), fat.size() * sizeof(double), cudaMemcpyHostToDevice));
     }
     CU(cudaMalloc((void**)&d.box, std::max<size_t>(32, tree.box.size() * sizeof(float))));
     if (!tree.box.empty()) CU(cudaMemcpy(d.box, tree.box.data(), tree.box.size() * sizeof(float), cudaMemcpyHostToDevice));
@@ -315,7 +328,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 16 + tree.box.size() * sizeof(float) +
+    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * (16 + 32) + tree.box.size() * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));

@@ -42,6 +42,8 @@ struct DeviceGrid {
   int n_leaves = 0, n_internal = 0, n_sm_nodes = 0;
   int depth = 0;                   // levels of internal nodes = level of the deepest leaf
   double2* node = nullptr;         // n_internal x {split value, bits(split dimension)}, heap order
+  double* fat = nullptr;           // n_internal x {split, left child's split, right child's split, bits(3 x 2-bit dimension)}:
+                                   // one 32-byte load decides two levels of a descent
   double* centers4 = nullptr;      // n_leaves x {x[LEAF], y[LEAF], z[LEAF]} (192-byte leaf blocks); padding slots = +inf
   float* box = nullptr;            // (n_internal + n_leaves) x 8 floats: tight box of the centres below each node
   // mesh

@@ -36,6 +36,9 @@ constexpr int QUERY_THREADS = IU_QUERY_THREADS;
                            // = every level through L1 (ld.global.nc): one load path, no branch, more L1 for the records
 #endif
 constexpr int MAX_SM_NODES = IU_SM_NODES > 0 ? IU_SM_NODES : 1;
+#ifndef IU_FAT_NODES
+#define IU_FAT_NODES 1   // 1: descents read {node, both children} per 32-byte load: one dependent load per two levels
+#endif
 #ifndef IU_SELP
 #define IU_SELP 1          // 1: branch-free selection of the query coordinate of a node's split dimension
 #endif
@@ -367,6 +370,7 @@ __global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lo
 // ------------------------------------------------------------------------------------------------
 struct TreeView {
   const double2* node;   // {split value, bits(split dimension)} per internal node, heap order
+  const double* fat;     // {split, left child's split, right child's split, bits(3 dims)} per internal node
   const double* centers4;   // leaf blocks of 24 doubles: x[8], y[8], z[8] (padding slots = +inf)
   const int32_t* orig_of_dev;   // original id per slot: read only to break exact distance ties
   const float* box;      // 8 floats per node (internal and leaf): tight box of the centres below it
@@ -482,6 +486,26 @@ __device__ __forceinline__ void nn_begin(const TreeView& t, const double* s_spli
   L.st = NNState{__longlong_as_double(0x7ff0000000000000LL), -1};
   L.pending = 0;
   int node = 0, lvl = 0;
+#if IU_FAT_NODES
+  {
+    auto step = [&](double s, int k) -> int {
+      const double qk = select3(qx, qy, qz, k);
+      const double d = qk - s;
+      lb[lvl * QUERY_THREADS] = __double2float_rd(d * d);
+      const int bit = qk < s ? 0 : 1;
+      node = 2 * node + 1 + bit;
+      ++lvl;
+      return bit;
+    };
+    while (node < t.n_internal) {
+      const D4 f = ld256(t.fat + 4 * (size_t)node);
+      const int dims = __double2loint(f.w);
+      const int b0 = step(f.x, dims & 3);
+      if (node >= t.n_internal) break;
+      step(b0 ? f.z : f.y, (dims >> (2 + 2 * b0)) & 3);
+    }
+  }
+#else
   while (node < t.n_internal) {
     double s; int k;
     fetch_node(t.node, t.n_sm_nodes, s_split, s_dim, node, s, k);
@@ -491,6 +515,7 @@ __device__ __forceinline__ void nn_begin(const TreeView& t, const double* s_spli
     node = 2 * node + (qk < s ? 1 : 2);
     ++lvl;
   }
+#endif
   scan_leaf(t, node, qx, qy, qz, L.st);
   const float bf = __double2float_ru(L.st.best);
   for (int l = 0; l < lvl; ++l)
@@ -522,6 +547,28 @@ __device__ __forceinline__ bool nn_round(const TreeView& t, const double* s_spli
     }
   }
   if (found) {
+#if IU_FAT_NODES
+    {
+      auto step = [&](double s, int k) -> int {
+        const double qk = select3(qx, qy, qz, k);
+        const double d = qk - s;
+        const double d2 = d * d;
+        lb[lvl * QUERY_THREADS] = __double2float_rd(d2);
+        if (!(d2 > L.st.best)) pending |= 1u << lvl;
+        const int bit = qk < s ? 0 : 1;
+        node = 2 * node + 1 + bit;
+        ++lvl;
+        return bit;
+      };
+      while (node < t.n_internal) {
+        const D4 f = ld256(t.fat + 4 * (size_t)node);
+        const int dims = __double2loint(f.w);
+        const int b0 = step(f.x, dims & 3);
+        if (node >= t.n_internal) break;
+        step(b0 ? f.z : f.y, (dims >> (2 + 2 * b0)) & 3);
+      }
+    }
+#else
     while (node < t.n_internal) {
       double s; int k;
       fetch_node(t.node, t.n_sm_nodes, s_split, s_dim, node, s, k);
@@ -533,6 +580,7 @@ __device__ __forceinline__ bool nn_round(const TreeView& t, const double* s_spli
       node = 2 * node + (qk < s ? 1 : 2);
       ++lvl;
     }
+#endif
     scan_leaf(t, node, qx, qy, qz, L.st);
   }
   L.node = node; L.lvl = lvl; L.pending = pending;
@@ -1257,7 +1305,7 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   QueryKernelParams P;
-  P.tree = TreeView{g.node, g.centers4, g.orig_of_dev, g.box, g.n_internal, g.n_sm_nodes < MAX_SM_NODES ? g.n_sm_nodes : MAX_SM_NODES};
+  P.tree = TreeView{g.node, g.fat, g.centers4, g.orig_of_dev, g.box, g.n_internal, g.n_sm_nodes < MAX_SM_NODES ? g.n_sm_nodes : MAX_SM_NODES};
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
