@@ -171,7 +171,7 @@ void collect_timings(iu_b200_grid* g) {
 }
 
 void free_device_grid(DeviceGrid& d) {
-  cudaFree(d.node); cudaFree(d.fat); cudaFree(d.box); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
+  cudaFree(d.fat); cudaFree(d.box); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
   cudaFree(d.orig_of_dev); cudaFree(d.pd); cudaFree(d.cd); cudaFree(d.icd); cudaFree(d.counters);
   d = DeviceGrid();
 }
@@ -265,11 +265,9 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     std::vector<double>().swap(h_centers);
     d.n_leaves = tree.n_leaves;
     d.n_internal = tree.n_leaves - 1;
-    d.n_sm_nodes = std::min(d.n_internal, 2047);
     for (int l = 1; l < tree.n_leaves; l <<= 1) ++g->tree_depth;
     d.depth = g->tree_depth;
     const size_t n_slots = (size_t)tree.n_leaves * LEAF;
-    CU(cudaMalloc((void**)&d.node, std::max<size_t>(1, d.n_internal) * sizeof(double2)));
     CU(cudaMalloc((void**)&d.orig_of_dev, n_slots * 4));
     CU(cudaMalloc((void**)&d.dev_of_orig, ((size_t)n_cells + 1) * 4));
     CU(cudaMalloc((void**)&d.centers4, n_slots * 24));
@@ -278,16 +276,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     CU(cudaMemsetAsync(d.counters, 0, CNT_N * sizeof(unsigned long long), s));
     CU(cudaMemsetAsync(d.dev_of_orig, 0, ((size_t)n_cells + 1) * 4, s));
     if (d.n_internal > 0) {
-      // interleave {split, bits(dim)}: one 16-byte load per tree level on the device
-      std::vector<double2> nodes((size_t)d.n_internal);
-      for (int i = 0; i < d.n_internal; ++i) {
-        const long long dim = tree.sdim[i];
-        double bits;
-        std::memcpy(&bits, &dim, 8);
-        nodes[i] = make_double2(tree.split[i], bits);
-      }
-      CU(cudaMemcpy(d.node, nodes.data(), nodes.size() * sizeof(double2), cudaMemcpyHostToDevice));
-      // the same nodes with their children's splits alongside: {split, split(2i+1), split(2i+2), dimensions}
+      // nodes with their children's splits alongside: {split, split(2i+1), split(2i+2), dimensions}
       std::vector<double> fat((size_t)4 * d.n_internal, 0.0);
       for (int i = 0; i < d.n_internal; ++i) {
         unsigned long long dims = tree.sdim[i];
@@ -328,7 +317,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * (16 + 32) + tree.box.size() * sizeof(float) +
+    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + tree.box.size() * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));

@@ -39,9 +39,8 @@ enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_EARLY = 3,
 struct DeviceGrid {
   int cell_type = 0, ppc = 0, n_cells = 0, n_points = 0;
   // kd-tree
-  int n_leaves = 0, n_internal = 0, n_sm_nodes = 0;
+  int n_leaves = 0, n_internal = 0;
   int depth = 0;                   // levels of internal nodes = level of the deepest leaf
-  double2* node = nullptr;         // n_internal x {split value, bits(split dimension)}, heap order
   double* fat = nullptr;           // n_internal x {split, left child's split, right child's split, bits(3 x 2-bit dimension)}:
                                    // one 32-byte load decides two levels of a descent
   double* centers4 = nullptr;      // n_leaves x {x[LEAF], y[LEAF], z[LEAF]} (192-byte leaf blocks); padding slots = +inf

@@ -31,14 +31,6 @@ constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #ifndef IU_QUERY_MIN_BLOCKS
 #define IU_QUERY_MIN_BLOCKS 4   // resident CTAs per SM the hot kernel is compiled for (64 registers per thread)
 #endif
-#ifndef IU_SM_NODES
-#define IU_SM_NODES 0      // tree nodes (top levels) staged in shared memory; 0 (default, measured faster: 16.95 -> 15.99 ms)
-                           // = every level through L1 (ld.global.nc): one load path, no branch, more L1 for the records
-#endif
-constexpr int MAX_SM_NODES = IU_SM_NODES > 0 ? IU_SM_NODES : 1;
-#ifndef IU_FAT_NODES
-#define IU_FAT_NODES 1   // 1: descents read {node, both children} per 32-byte load: one dependent load per two levels
-#endif
 #ifndef IU_SELP
 #define IU_SELP 1          // 1: branch-free selection of the query coordinate of a node's split dimension
 #endif
@@ -47,6 +39,9 @@ constexpr int MAX_SM_NODES = IU_SM_NODES > 0 ? IU_SM_NODES : 1;
 // so that they do not push the cell records of the current Morton window out of L2.
 #ifndef IU_WALK_256
 #define IU_WALK_256 0   // 1: 32-byte loads in the walk too (6 instead of 12 per cell, but spills at 64 registers: slower)
+#endif
+#ifndef IU_HILBERT
+#define IU_HILBERT 1    // 1: queries of 3-D meshes are ordered along a Hilbert curve, 0: Morton order
 #endif
 #ifndef IU_NODE_BOX
 #define IU_NODE_BOX 1   // 1: test the far child's tight centre box before descending into it (nearest_center)
@@ -346,36 +341,69 @@ __device__ __forceinline__ uint32_t quantise(double x, double lo, double scale, 
   return t >= (double)maxv ? maxv : (uint32_t)t;
 }
 
-// bits = bits per dimension; planar meshes (z extent 0) use a 2-D key
+// One level of the 3-D Hilbert curve as a table: entry [state * 8 + octant] = digit | next state << 3, where
+// octant = x | y << 1 | z << 2 bits of that level and state = 3 * e + d of the compact-Hilbert-index recurrence
+// (entry point e in 0..7, direction d in 0..2): 24 states x 8 octants.  Any continuous space-filling order would do -
+// the order only decides which queries share a warp and an L2 window, never a result.
+__device__ __forceinline__ uint32_t hilbert_table_entry(int state, int octant) {
+  auto rotr = [](int x, int i) { i %= 3; return ((x >> i) | (x << (3 - i))) & 7; };
+  auto rotl = [](int x, int i) { i %= 3; return ((x << i) | (x >> (3 - i))) & 7; };
+  auto trailing_ones = [](int x) { return __ffs(~x) - 1; };
+  const int e = state / 3, d = state % 3;
+  const int l = rotr(octant ^ e, d + 1);
+  const int w = l ^ (l >> 1) ^ (l >> 2);                               // inverse Gray code = digit
+  const int ent = w == 0 ? 0 : (((w - 1) & ~1) ^ (((w - 1) & ~1) >> 1));   // entry point of sub-cube w
+  const int dir = w == 0 ? 0 : (w & 1 ? trailing_ones(w) : trailing_ones(w - 1)) % 3;
+  const int e2 = e ^ rotl(ent, d + 1), d2 = (d + dir + 1) % 3;
+  return (uint32_t)(w | ((3 * e2 + d2) << 3));
+}
+
+// bits = bits per dimension; planar meshes (z extent 0) use a 2-D Morton key, the others a Hilbert key
+// (IU_HILBERT = 0: Morton)
 __global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lox, double loy, double loz, double sx,
                               double sy, double sz, int bits, int planar, uint32_t* __restrict__ keys,
                               uint32_t* __restrict__ idx) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const uint32_t maxv = (1u << bits) - 1u;
-  const uint32_t ix = quantise(__ldg(r + 3 * i), lox, sx, maxv);
-  const uint32_t iy = quantise(__ldg(r + 3 * i + 1), loy, sy, maxv);
-  uint32_t key;
-  if (planar) key = spread2(ix) | (spread2(iy) << 1);
-  else {
-    const uint32_t iz = quantise(__ldg(r + 3 * i + 2), loz, sz, maxv);
-    key = spread3(ix) | (spread3(iy) << 1) | (spread3(iz) << 2);
+#if IU_HILBERT
+  __shared__ uint8_t s_tab[192];
+  if (!planar) {
+    for (int t = threadIdx.x; t < 192; t += blockDim.x) s_tab[t] = (uint8_t)hilbert_table_entry(t >> 3, t & 7);
+    __syncthreads();
   }
-  keys[i] = key;
-  idx[i] = (uint32_t)i;
+#endif
+  const uint32_t maxv = (1u << bits) - 1u;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t ix = quantise(__ldg(r + 3 * i), lox, sx, maxv);
+    const uint32_t iy = quantise(__ldg(r + 3 * i + 1), loy, sy, maxv);
+    uint32_t key;
+    if (planar) key = spread2(ix) | (spread2(iy) << 1);
+    else {
+      const uint32_t iz = quantise(__ldg(r + 3 * i + 2), loz, sz, maxv);
+      key = spread3(ix) | (spread3(iy) << 1) | (spread3(iz) << 2);
+#if IU_HILBERT
+      uint32_t h = 0, state = 0;
+      for (int l = 3 * (bits - 1); l >= 0; l -= 3) {
+        const uint32_t t = s_tab[state * 8 + ((key >> l) & 7u)];
+        h = (h << 3) | (t & 7u);
+        state = t >> 3;
+      }
+      key = h;
+#endif
+    }
+    keys[i] = key;
+    idx[i] = (uint32_t)i;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
 // device-side pieces of the hot path
 // ------------------------------------------------------------------------------------------------
 struct TreeView {
-  const double2* node;   // {split value, bits(split dimension)} per internal node, heap order
-  const double* fat;     // {split, left child's split, right child's split, bits(3 dims)} per internal node
+  const double* fat;     // per internal node (heap order) {split, left child's split, right child's split, bits(3 x 2-bit
+                         // split dimension)}: one 32-byte load decides two levels of a descent
   const double* centers4;   // leaf blocks of 24 doubles: x[8], y[8], z[8] (padding slots = +inf)
   const int32_t* orig_of_dev;   // original id per slot: read only to break exact distance ties
   const float* box;      // 8 floats per node (internal and leaf): tight box of the centres below it
   int n_internal;
-  int n_sm_nodes;
 };
 
 // Exact nearest centre (squared distance summed x, y, z without FMA, like kdtree2's leaf loop);
@@ -406,15 +434,6 @@ __device__ __forceinline__ double select3(double qx, double qy, double qz, int k
 #else
   return k == 0 ? qx : (k == 1 ? qy : qz);
 #endif
-}
-
-__device__ __forceinline__ void fetch_node(const double2* __restrict__ nodes, int n_sm_nodes, const double* s_split,
-                                           const uint8_t* s_dim, int node, double& s, int& k) {
-#if IU_SM_NODES > 0
-  if (node < n_sm_nodes) { s = s_split[node]; k = s_dim[node]; return; }
-#endif
-  const double2 nd = __ldg(nodes + node);
-  s = nd.x; k = __double2loint(nd.y);
 }
 
 struct NNState {
@@ -481,12 +500,11 @@ struct NNLane {
 
 // first descent (best = +inf, every level stays pending), first leaf, then the filter of all levels
 // against the first `best`: all of it runs with the lanes converged
-__device__ __forceinline__ void nn_begin(const TreeView& t, const double* s_split, const uint8_t* s_dim, float* lb, double qx,
+__device__ __forceinline__ void nn_begin(const TreeView& t, float* lb, double qx,
                                          double qy, double qz, NNLane& L) {
   L.st = NNState{__longlong_as_double(0x7ff0000000000000LL), -1};
   L.pending = 0;
   int node = 0, lvl = 0;
-#if IU_FAT_NODES
   {
     auto step = [&](double s, int k) -> int {
       const double qk = select3(qx, qy, qz, k);
@@ -505,17 +523,6 @@ __device__ __forceinline__ void nn_begin(const TreeView& t, const double* s_spli
       step(b0 ? f.z : f.y, (dims >> (2 + 2 * b0)) & 3);
     }
   }
-#else
-  while (node < t.n_internal) {
-    double s; int k;
-    fetch_node(t.node, t.n_sm_nodes, s_split, s_dim, node, s, k);
-    const double qk = select3(qx, qy, qz, k);
-    const double d = qk - s;
-    lb[lvl * QUERY_THREADS] = __double2float_rd(d * d);
-    node = 2 * node + (qk < s ? 1 : 2);
-    ++lvl;
-  }
-#endif
   scan_leaf(t, node, qx, qy, qz, L.st);
   const float bf = __double2float_ru(L.st.best);
   for (int l = 0; l < lvl; ++l)
@@ -525,7 +532,7 @@ __device__ __forceinline__ void nn_begin(const TreeView& t, const double* s_spli
 
 // One backtracking round: pop the deepest pending level whose plane bound and far-child box still
 // pass, descend from the far child to a leaf, scan it.  false = nothing left, the search is done.
-__device__ __forceinline__ bool nn_round(const TreeView& t, const double* s_split, const uint8_t* s_dim, float* lb, double qx,
+__device__ __forceinline__ bool nn_round(const TreeView& t, float* lb, double qx,
                                          double qy, double qz, NNLane& L) {
   const float bf = __double2float_ru(L.st.best);
   int node = L.node, lvl = L.lvl;
@@ -547,7 +554,6 @@ __device__ __forceinline__ bool nn_round(const TreeView& t, const double* s_spli
     }
   }
   if (found) {
-#if IU_FAT_NODES
     {
       auto step = [&](double s, int k) -> int {
         const double qk = select3(qx, qy, qz, k);
@@ -568,31 +574,18 @@ __device__ __forceinline__ bool nn_round(const TreeView& t, const double* s_spli
         step(b0 ? f.z : f.y, (dims >> (2 + 2 * b0)) & 3);
       }
     }
-#else
-    while (node < t.n_internal) {
-      double s; int k;
-      fetch_node(t.node, t.n_sm_nodes, s_split, s_dim, node, s, k);
-      const double qk = select3(qx, qy, qz, k);
-      const double d = qk - s;
-      const double d2 = d * d;
-      lb[lvl * QUERY_THREADS] = __double2float_rd(d2);
-      if (!(d2 > L.st.best)) pending |= 1u << lvl;
-      node = 2 * node + (qk < s ? 1 : 2);
-      ++lvl;
-    }
-#endif
     scan_leaf(t, node, qx, qy, qz, L.st);
   }
   L.node = node; L.lvl = lvl; L.pending = pending;
   return found;
 }
 
-__device__ __forceinline__ int nearest_center(const TreeView& t, const double* s_split, const uint8_t* s_dim, float* s_lb,
+__device__ __forceinline__ int nearest_center(const TreeView& t, float* s_lb,
                                               double qx, double qy, double qz) {
   float* lb = s_lb + threadIdx.x;   // lb[l * QUERY_THREADS]
   NNLane L;
-  nn_begin(t, s_split, s_dim, lb, qx, qy, qz, L);
-  while (nn_round(t, s_split, s_dim, lb, qx, qy, qz, L)) {}
+  nn_begin(t, lb, qx, qy, qz, L);
+  while (nn_round(t, lb, qx, qy, qz, L)) {}
   return L.st.besti;
 }
 
@@ -872,16 +865,7 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
 // spread is inside a round (descent lengths, pop loops), not in the number of rounds: 18.9 vs 15.4 ms.
 template <int CT, int MODE, int NV, int SCHED>
 __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(const QueryKernelParams P) {
-  __shared__ double s_split[MAX_SM_NODES];
-  __shared__ uint8_t s_dim[MAX_SM_NODES + 1];
   extern __shared__ float s_lb[];   // [tree depth][QUERY_THREADS] plane-distance lower bounds (nearest_center)
-  if (MODE != QM_INTERP_ICELL && IU_SM_NODES > 0) {
-    for (int i = threadIdx.x; i < P.tree.n_sm_nodes; i += blockDim.x) {
-      const double2 nd = P.tree.node[i];
-      s_split[i] = nd.x; s_dim[i] = (uint8_t)__double2loint(nd.y);
-    }
-    __syncthreads();
-  }
   // SCHED = 1: warps draw STILE consecutive (sorted) queries at a time from the ticket counter
 #ifndef IU_STILE
 #define IU_STILE 128
@@ -919,7 +903,7 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       }
     }
     if (MODE == QM_NEAREST) {
-      const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
+      const int slot = nearest_center(P.tree, s_lb, qx, qy, qz);
       ST_STREAM(P.out_i32 + i, slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0);
       continue;
     }
@@ -930,7 +914,7 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       if (h < 1) { atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
       start = __ldg(P.dev_of_orig + h);
     } else if (h < 1) {                                                                // :422-423
-      const int slot = nearest_center(P.tree, s_split, s_dim, s_lb, qx, qy, qz);
+      const int slot = nearest_center(P.tree, s_lb, qx, qy, qz);
       if (slot < 0) { ST_STREAM(P.i_cell + i, 0); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
       start = slot + 1;
     } else {
@@ -1294,7 +1278,7 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
   const double nb = (double)(1u << bits);
   double sc[3];
   for (int k = 0; k < 3; ++k) { const double ext = g.rmax[k] - g.rmin[k]; sc[k] = ext > 0 ? nb / ext : 0.0; }
-  k_morton_keys<<<blocks_for(n, 256), 256, 0, s>>>(n, r, g.rmin[0], g.rmin[1], g.rmin[2], sc[0], sc[1], sc[2], bits, planar, keys, idx);
+  k_morton_keys<<<(unsigned)std::min<int64_t>(blocks_for(n, 256), 148 * 32), 256, 0, s>>>(n, r, g.rmin[0], g.rmin[1], g.rmin[2], sc[0], sc[1], sc[2], bits, planar, keys, idx);
   const int end_bit = planar ? 2 * bits : 3 * bits;
   cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const uint32_t*)keys, keys_alt, (const uint32_t*)idx, idx_alt, n, 0, end_bit, s);
   if (end_bit_out) *end_bit_out = end_bit;
@@ -1305,7 +1289,7 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   QueryKernelParams P;
-  P.tree = TreeView{g.node, g.fat, g.centers4, g.orig_of_dev, g.box, g.n_internal, g.n_sm_nodes < MAX_SM_NODES ? g.n_sm_nodes : MAX_SM_NODES};
+  P.tree = TreeView{g.fat, g.centers4, g.orig_of_dev, g.box, g.n_internal};
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
