@@ -69,7 +69,7 @@ extern "C" {
 #define IU_B200_STAT_NOT_FOUND 6       /* queries that ended with i_cell <= 0 */
 #define IU_B200_STAT_QUERY_KERNEL_NS 7  /* with IU_B200_OPT_TIME_KERNELS: summed device time of the hot kernel */
 #define IU_B200_STAT_QUERY_KERNEL_LAUNCHES 8
-#define IU_B200_STAT_SORT_NS 9         /* same for Morton keys + radix sort */
+#define IU_B200_STAT_SORT_NS 9         /* same for curve keys + radix sort */
 #define IU_B200_N_STATS 12
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */
