@@ -40,9 +40,6 @@ constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #ifndef IU_WALK_256
 #define IU_WALK_256 0   // 1: 32-byte loads in the walk too (6 instead of 12 per cell, but spills at 64 registers: slower)
 #endif
-#ifndef IU_PREFETCH_NEXT
-#define IU_PREFETCH_NEXT 0   // 1: prefetch the coordinates and hint of the lane's next query of the tile
-#endif
 #ifndef IU_HILBERT
 #define IU_HILBERT 1    // 1: queries of 3-D meshes are ordered along a Hilbert curve, 0: Morton order
 #endif
@@ -892,15 +889,6 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       if (t >= P.n) continue;
     } else if (t >= P.n) break;
     const int64_t i = P.perm ? (int64_t)LD_STREAM(P.perm + t) : t;
-#if IU_PREFETCH_NEXT
-    // the next query of this lane (same tile, 32 further on): start its scattered reads now
-    if (SCHED && P.perm && sub < STILE / 32 && t + 32 < P.n) {
-      const int64_t i2 = (int64_t)LD_STREAM(P.perm + t + 32);
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(P.r + 3 * i2));
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(P.r + 3 * i2 + 2));
-      if (MODE != QM_NEAREST) asm volatile("prefetch.global.L1 [%0];" ::"l"(P.i_cell + i2));
-    }
-#endif
     // a query's 24 bytes as two scattered loads instead of three: 16 + 8 or 8 + 16 bytes, whichever is aligned
     double qx, qy, qz;
     {
