@@ -49,7 +49,11 @@ extern "C" {
 #define IU_B200_CELL_WALK_LIMIT (-2)
 
 /* options for iu_b200_set_option */
-#define IU_B200_OPT_SORT_QUERIES 1  /* 0 never, 1 always, 2 auto (default): Morton-sort batches;
+#define IU_B200_OPT_SORT_QUERIES 1  /* 0 never, 1 always, 2 auto (default): sort batches along a space-filling curve
+                                       (auto: point queries always; rays of iu_get_cell_through_neighbors in calls
+                                       of >= 2^20 rays when the latest sample of ray lengths is above ~half a mean
+                                       cell size - the grid's first such call waits for its sample, later ones use
+                                       the latest sample that has arrived and stay asynchronous);
                                        3 = the caller's queries are already in a spatially coherent
                                        order (no sort, no permutation, ticket-tile scheduling) */
 #define IU_B200_OPT_MAX_WALK_STEPS 2 /* step cap used where the reference passes huge(1); default 2^20 */

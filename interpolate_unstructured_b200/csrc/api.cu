@@ -94,6 +94,11 @@ struct iu_b200_grid {
   // sort workspace (device API and host pipeline share it: all compute is stream-ordered by the caller)
   DevBuf<uint32_t> keys, keys_alt, idx, idx_alt;
   DevBuf<char> sort_temp;
+  // ray-walk sort decision (IU_B200_OPT_SORT_QUERIES = 2): mean sampled ray length of the latest measured call
+  DevBuf<double> walk_sum;
+  double* h_walk_sum = nullptr;   // pinned
+  cudaEvent_t walk_ev = nullptr;
+  bool walk_ev_pending = false, walk_measured = false, walk_sort = false;
   // tracer workspace: seeds (3, n), their field (ndim, n) and cells
   DevBuf<double> tr_seed, tr_field;
   DevBuf<int32_t> tr_cell;
@@ -389,7 +394,9 @@ int iu_b200_grid_destroy(iu_b200_grid* g) {
       sl.i_a.release(); sl.i_b.release(); sl.i_c.release(); sl.i_d.release();
     }
     g->keys.release(); g->keys_alt.release(); g->idx.release(); g->idx_alt.release(); g->sort_temp.release();
-    g->tr_seed.release(); g->tr_field.release(); g->tr_cell.release();
+    g->tr_seed.release(); g->tr_field.release(); g->tr_cell.release(); g->walk_sum.release();
+    if (g->h_walk_sum) cudaFreeHost(g->h_walk_sum);
+    if (g->walk_ev) cudaEventDestroy(g->walk_ev);
     if (g->s_in) cudaStreamDestroy(g->s_in);
     if (g->s_comp) cudaStreamDestroy(g->s_comp);
     if (g->s_out) cudaStreamDestroy(g->s_out);
@@ -736,9 +743,45 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
 // IU_B200_OPT_SORT_QUERIES = 1 are they processed in Morton order of the start positions: measured on
 // C4 (100M rays), the 13 scattered accesses per ray through the permutation cost more than the
 // locality gains below ~2 cells per ray (18.5 -> 29.7 ms at 0.1 h) and pay off above (71 -> 32.6 ms at 1 h).
+constexpr int64_t WALK_AUTO_MIN_RAYS = 1 << 20;
+constexpr int WALK_AUTO_SAMPLES = 4096;
+constexpr double WALK_AUTO_CELLS = 0.55;
+
 void run_walk(iu_b200_grid* g, WalkArgs a, cudaStream_t s) {
   const int64_t n = a.n;
   const int64_t step = g->dev_batch;
+  // auto: sorting pays once the rays cross more than about one cell (profiles/README.md, C4 table: unsorted
+  // 0.13 + 0.31 d ns per ray, sorted 0.29 + 0.02 d, d = ray length in mean cell sizes).  d comes from a sample of a
+  // call's rays, read back asynchronously: the first large call waits for its own sample, later calls use the latest
+  // sample that has arrived (tracers call with similar rays step after step) and never synchronise the stream.
+  bool auto_sort = false;
+  if (g->sort_mode == 2 && n >= WALK_AUTO_MIN_RAYS) {
+    const DeviceGrid& dg = g->dg;
+    double ext = 1.0; int nd = 0;
+    for (int k = 0; k < 3; ++k) if (dg.rmax[k] > dg.rmin[k]) { ext *= dg.rmax[k] - dg.rmin[k]; ++nd; }
+    if (nd >= 2 && dg.n_cells > 0) {
+      const double h_cell = std::pow(ext / dg.n_cells, 1.0 / nd);
+      if (!g->h_walk_sum) {
+        CU(cudaHostAlloc((void**)&g->h_walk_sum, sizeof(double), cudaHostAllocDefault));
+        CU(cudaEventCreateWithFlags(&g->walk_ev, cudaEventDisableTiming));
+        g->walk_sum.ensure(1);
+      }
+      auto take = [&]() {
+        g->walk_sort = *g->h_walk_sum / WALK_AUTO_SAMPLES > WALK_AUTO_CELLS * h_cell;
+        g->walk_ev_pending = false;
+        g->walk_measured = true;
+      };
+      if (g->walk_ev_pending && cudaEventQuery(g->walk_ev) == cudaSuccess) take();
+      if (!g->walk_ev_pending) {
+        g->n_launches += launch_ray_length_sample(n, WALK_AUTO_SAMPLES, a.r0, a.r1, g->walk_sum.p, s);
+        CU(cudaMemcpyAsync(g->h_walk_sum, g->walk_sum.p, sizeof(double), cudaMemcpyDeviceToHost, s));
+        CU(cudaEventRecord(g->walk_ev, s));
+        g->walk_ev_pending = true;
+      }
+      if (!g->walk_measured) { CU(cudaEventSynchronize(g->walk_ev)); take(); }
+      auto_sort = g->walk_sort;
+    }
+  }
   for (int64_t off = 0; off < n; off += step) {
     const int64_t m = std::min(step, n - off);
     WalkArgs b = a;
@@ -746,7 +789,8 @@ void run_walk(iu_b200_grid* g, WalkArgs a, cudaStream_t s) {
     b.r0 = a.r0 + 3 * off; b.r1 = a.r1 + 3 * off; b.ic0 = a.ic0 + off; b.ic1 = a.ic1 + off;
     b.r_p = a.r_p + 3 * off; b.n_steps = a.n_steps + off; b.status = a.status + off;
     b.perm = nullptr;
-    if (g->sort_mode == 1 && m > 1) {
+    const bool sort = m > 1 && (g->sort_mode == 1 || auto_sort);
+    if (sort) {
       const int end_bit = morton_end_bit(g->dg);
       g->keys.ensure(m); g->keys_alt.ensure(m); g->idx.ensure(m); g->idx_alt.ensure(m);
       g->sort_temp.ensure(sort_temp_bytes(m, end_bit));

@@ -128,6 +128,7 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
 int morton_end_bit(const DeviceGrid& g);
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s);
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s);
+int launch_ray_length_sample(int64_t n, int n_samples, const double* r0, const double* r1, double* sum, cudaStream_t s);
 int launch_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const double* y, double* r, cudaStream_t s);
 int launch_trace(const DeviceGrid& g, const TraceArgs& a, cudaStream_t s);
 int launch_generate_queries(int64_t n, int64_t first, uint64_t seed, const double lo[3], const double hi[3], double* r,

@@ -1332,6 +1332,27 @@ int launch_trace(const DeviceGrid& g, const TraceArgs& a, cudaStream_t s) {
   return 1;
 }
 
+// sum of |r1 - r0| over n_samples rays spread evenly over the batch (run_walk's sort decision)
+__global__ void k_ray_length_sample(int64_t n, int n_samples, const double* __restrict__ r0, const double* __restrict__ r1,
+                                    double* __restrict__ sum) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  double len = 0.0;
+  if (j < n_samples) {
+    const int64_t i = (int64_t)((double)j * (double)n / (double)n_samples);
+    const double dx = r1[3 * i] - r0[3 * i], dy = r1[3 * i + 1] - r0[3 * i + 1], dz = r1[3 * i + 2] - r0[3 * i + 2];
+    len = sqrt(dx * dx + dy * dy + dz * dz);
+    if (!(len < 1.0e300)) len = 0.0;   // NaN / inf rays do not vote
+  }
+  for (int o = 16; o > 0; o >>= 1) len += __shfl_down_sync(0xffffffffu, len, o);
+  if ((threadIdx.x & 31) == 0) atomicAdd(sum, len);
+}
+
+int launch_ray_length_sample(int64_t n, int n_samples, const double* r0, const double* r1, double* sum, cudaStream_t s) {
+  cudaMemsetAsync(sum, 0, sizeof(double), s);
+  k_ray_length_sample<<<(n_samples + 255) / 256, 256, 0, s>>>(n, n_samples, r0, r1, sum);
+  return 1;
+}
+
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   const int32_t* mask = a.mask_col >= 0 ? g.icd + (size_t)a.mask_col * g.n_cells : nullptr;

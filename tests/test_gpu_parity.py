@@ -294,6 +294,33 @@ def test_walk_batch_sorted_and_unsorted_agree_with_oracle():
     assert (exp[3] == -1).sum() > 10 and (exp[3] == 1).sum() > 100 and (exp[3] == 0).sum() > 100
 
 
+def test_walk_batch_auto_sort_decision():
+    """IU_B200_OPT_SORT_QUERIES = 2 (default): large batches of rays are sorted only when the latest sample of ray lengths is above
+    about half a mean cell size; either way the results are the bits of the unsorted walk."""
+    g, o, pts = _both_from_mesh("tetra", 10, n_vars=1, cell_data=True)
+    n = (1 << 20) + 1000
+    r0 = _queries(pts, n, 77)
+    ic0 = g.iu_get_cell(r0)
+    assert (ic0 >= 1).all()
+    h_cell = (np.prod(pts.max(0) - pts.min(0)) / g.n_cells) ** (1 / 3)
+    rng = np.random.default_rng(5)
+    d = rng.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    g.set_option(api.OPT_HOST_CHUNK, 1 << 21)
+    g.set_option(api.OPT_TIME_KERNELS, 1)
+    for length, sorted_expected in ((0.1 * h_cell, False), (2.0 * h_cell, True)):
+        r1 = r0 + length * d
+        g.set_option(api.OPT_SORT_QUERIES, 0)
+        exp = g.iu_get_cell_through_neighbors(50, r0, r1, ic0)
+        g.set_option(api.OPT_SORT_QUERIES, 2)
+        g.iu_get_cell_through_neighbors(50, r0, r1, ic0)       # its sample decides for the calls that follow
+        g.reset_stats()
+        got = g.iu_get_cell_through_neighbors(50, r0, r1, ic0)
+        assert (g.stats()["sort_ns"] > 0) == sorted_expected
+        for a, b in zip(got, exp):
+            assert np.array_equal(a, b, equal_nan=True)
+
+
 def test_error_behaviour():
     g, o, pts = _both_from_mesh("tetra", 4, n_vars=2)
     r = _queries(pts, 100, 1)
