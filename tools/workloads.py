@@ -96,6 +96,8 @@ def run_c4(a):
     nb = api.build_cell_neighbors(cells, pts, "tetra")
     pd = meshgen.smooth_fields(pts, 3)
     g = api.Grid.from_arrays("tetra", pts, cells, nb, pd, device=0)
+    if os.environ.get("IU_WL_SORT"):            # A/B of IU_B200_OPT_SORT_QUERIES (default 2 = auto)
+        g.set_option(api.OPT_SORT_QUERIES, int(os.environ["IU_WL_SORT"]))
     nq = int(a.queries or 1e8)
     h = 1.0 / n
     r0 = torch.empty((nq, 3), dtype=torch.float64, device=dev)
