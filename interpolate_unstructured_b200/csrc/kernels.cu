@@ -10,9 +10,12 @@
 //   k_cell_centers     iu_get_cell_center for every cell (input of the kd-tree build)
 //   k_build_records    set_cell_points + set_face_normal_vectors + set_cell_volumes -> 256/192-B
 //                      per-cell records in kd-tree leaf order, plus the leaf centre blocks
-//   k_morton_keys      Morton key of each query for the coherence sort (cub radix sort follows)
+//   k_morton_keys      sort key of each query for the coherence sort: position of its key cell along a Hilbert curve
+//                      (3-D meshes) or the Z curve (planar meshes); cub radix sort follows
 //   k_query<...>       THE hot kernel: [kd-tree nearest centre | hint] -> ray walk -> interpolate
 //   k_walk<...>        iu_get_cell_through_neighbors with explicit r0 / ic0 / mask outputs
+//   k_ray_length_sample  mean ray length of a batch (decides whether k_walk processes it in sorted order)
+//   k_trace<...>       iu_integrate_along_field, one field line per thread
 //   k_pack_point_data, k_export_geometry, k_generate_queries: plumbing
 #include <cub/device/device_radix_sort.cuh>
 
@@ -35,8 +38,6 @@ constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #define IU_SELP 1          // 1: branch-free selection of the query coordinate of a node's split dimension
 #endif
 
-// Query inputs and results are touched exactly once per launch: mark them evict-first (ld/st .cs)
-// so that they do not push the cell records of the current Morton window out of L2.
 #ifndef IU_WALK_256
 #define IU_WALK_256 0   // 1: 32-byte loads in the walk too (6 instead of 12 per cell, but spills at 64 registers: slower)
 #endif
@@ -46,6 +47,8 @@ constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #ifndef IU_NODE_BOX
 #define IU_NODE_BOX 1   // 1: test the far child's tight centre box before descending into it (nearest_center)
 #endif
+// Query inputs and results are touched exactly once per launch: mark them evict-first (ld/st .cs)
+// so that they do not push the cell records of the current window of the sort order out of L2.
 #ifndef IU_STREAM_HINTS
 #define IU_STREAM_HINTS 1
 #endif
@@ -417,7 +420,11 @@ struct TreeView {
 //     current leaf by shifts) and descends again.  Pending bits always lie on the current
 //     root-to-leaf path, so no per-level node ids are kept;
 //   * the first descent and leaf scan run with the whole warp converged (uniform tree depth); the
-//     first pop is preceded by a convergent filter of all levels against the first `best`.
+//     first pop is preceded by a convergent filter of all levels against the first `best`;
+//   * a popped far child is entered only if the tight box of the centres below it (box_lower_bound)
+//     is within `best` as well;
+//   * descents read "fat" nodes {split, both children's splits, dimensions}: one dependent 32-byte
+//     load per two levels.
 // By monotonicity of fp64 subtraction, multiplication and addition, (q[dim]-split)^2 is a lower
 // bound of the COMPUTED squared distance of every centre behind the plane, and the float bound is
 // <= it, so pruning with '>' never drops the true fp64 minimum or a tie.  Returns the 0-based
