@@ -343,7 +343,8 @@ def run_b200(args):
                                    f"{N_VARS} vars, {nq} uniform queries per GPU per step, mesh replicated per GPU",
                        "queries_per_step_per_gpu": nq, "l2_policy": "inputs larger than L2 (24 B x queries per step >> 126 MB)",
                        "sort_queries": args.sort if args.sort >= 0 else 2, "dynamic_tiles": args.dynamic if args.dynamic >= 0 else 1, "setup_seconds": setup_s,
-                       "mesh_device_bytes": st["mesh_bytes"], "tree_depth": st["tree_depth"]},
+                       "mesh_device_bytes": st["mesh_bytes"], "tree_depth": st["tree_depth"],
+                       "nn_voxel_table": {k: st[k] for k in ("nn_voxels", "nn_voxels_tree", "nn_voxel_entries", "nn_tree_queries", "nn_voxel_build_us")}},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": gpu_launches, "clocks": clocks.summary(),
             "checks": {"located": n_found, "linear_field_max_abs_err": lin_err},
         }

@@ -63,6 +63,11 @@ extern "C" {
 #define IU_B200_OPT_DYNAMIC_TILES 6 /* 1 (default): sorted batches are handed to warps as tiles of consecutive
                                        queries from a device ticket counter; 0: static grid-stride assignment */
 
+#define IU_B200_OPT_NN_VOXEL_DENSITY 7 /* voxels of the nearest-centre table per 100 cells (default 400; 0 = no table,
+                                       every cold query searches the kd-tree).  The table lists, per voxel of a regular
+                                       grid over the mesh's bounding box, every centre that can be nearest to a point of
+                                       the voxel; results are identical with and without it.  Setting it rebuilds the table. */
+
 /* indices into the int64 array filled by iu_b200_get_stats */
 #define IU_B200_STAT_KERNEL_LAUNCHES 0 /* kernels of this library launched since creation/reset */
 #define IU_B200_STAT_WALK_LIMIT_HITS 1
@@ -74,7 +79,12 @@ extern "C" {
 #define IU_B200_STAT_QUERY_KERNEL_NS 7  /* with IU_B200_OPT_TIME_KERNELS: summed device time of the hot kernel */
 #define IU_B200_STAT_QUERY_KERNEL_LAUNCHES 8
 #define IU_B200_STAT_SORT_NS 9         /* same for curve keys + radix sort */
-#define IU_B200_N_STATS 12
+#define IU_B200_STAT_NN_VOXELS 10       /* voxels of the nearest-centre table (0 = none) */
+#define IU_B200_STAT_NN_VOXELS_TREE 11  /* voxels with too many candidates: their queries search the kd-tree */
+#define IU_B200_STAT_NN_VOXEL_ENTRIES 12 /* sum of the candidate-list lengths */
+#define IU_B200_STAT_NN_TREE_QUERIES 13 /* cold queries that searched the kd-tree although a table exists */
+#define IU_B200_STAT_NN_VOXEL_BUILD_US 14 /* device time of the last table build */
+#define IU_B200_N_STATS 16
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */
 

@@ -30,8 +30,10 @@ CELL_TYPES = {"triangle": TRIANGLE, "quad": QUAD, "tetra": TETRA}
 E_INVAL, E_CUDA, E_IO, E_HINT, E_NOMEM = -1, -2, -3, -4, -5
 CELL_WALK_LIMIT = -2
 OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KERNELS, OPT_DYNAMIC_TILES = 1, 2, 3, 4, 5, 6
+OPT_NN_VOXEL_DENSITY = 7
 STAT_NAMES = ["kernel_launches", "walk_limit_hits", "queries", "workspace_bytes", "mesh_bytes", "tree_depth",
-              "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "reserved10", "reserved11"]
+              "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "nn_voxels", "nn_voxels_tree", "nn_voxel_entries",
+              "nn_tree_queries", "nn_voxel_build_us", "reserved15"]
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)
@@ -379,7 +381,7 @@ class Grid:
         _check(lib().iu_b200_set_option(self._h, int(option), int(value)))
 
     def stats(self):
-        s = (C.c_int64 * 12)()
+        s = (C.c_int64 * len(STAT_NAMES))()
         _check(lib().iu_b200_get_stats(self._h, s))
         return dict(zip(STAT_NAMES, (int(x) for x in s)))
 

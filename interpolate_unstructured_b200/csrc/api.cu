@@ -6,7 +6,9 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -87,6 +89,10 @@ struct iu_b200_grid {
   int64_t host_chunk = 1 << 22;
   int64_t dev_batch = 1 << 26;
   int dynamic_tiles = 1;   // sorted sub-batches draw tiles of queries from a ticket counter (kernels.cu, SCHED = 1)
+  int voxel_density = 400; // voxels of the nearest-centre table per 100 cells (0 = no table, kd-tree search only)
+  double cmin[3] = {0, 0, 0}, cmax[3] = {0, 0, 0};   // bounds of the cell centres
+  int64_t vox_flagged = 0, vox_entries = 0;
+  double vox_build_ms = 0;
   // stats
   int64_t n_launches = 0, n_queries = 0;
   size_t mesh_bytes = 0;
@@ -176,6 +182,7 @@ void collect_timings(iu_b200_grid* g) {
 }
 
 void free_device_grid(DeviceGrid& d) {
+  cudaFree(d.cen32); cudaFree(d.vox_lists);
   cudaFree(d.fat); cudaFree(d.box); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
   cudaFree(d.orig_of_dev); cudaFree(d.pd); cudaFree(d.cd); cudaFree(d.icd); cudaFree(d.counters);
   d = DeviceGrid();
@@ -217,6 +224,77 @@ bool check_device_available() {
 // lifecycle
 // ------------------------------------------------------------------------------------------------
 namespace {
+
+// (Re)builds the voxel table of the nearest-centre search for g->voxel_density voxels per 100 cells (device.h:
+// VoxelGrid, kernels.cu: k_build_voxels).  The table is an accelerator only: without it (density 0, degenerate
+// boxes, not enough memory) every cold query runs the exact kd-tree search.
+void build_voxel_table(iu_b200_grid* g) {
+  DeviceGrid& d = g->dg;
+  if (d.vox_lists) { CU(cudaDeviceSynchronize()); cudaFree(d.vox_lists); }
+  d.vox_lists = nullptr;
+  d.vox = VoxelGrid();
+  d.n_vox = 0;
+  g->vox_flagged = g->vox_entries = 0;
+  g->vox_build_ms = 0;
+  if (g->voxel_density <= 0 || d.n_cells < 1) return;
+  VoxelGrid v;
+  int nd = 0;
+  double vol = 1.0;
+  for (int k = 0; k < 3; ++k) {
+    const double e = d.rmax[k] - d.rmin[k];
+    if (!(e >= 0.0) || !std::isfinite(e)) return;
+    v.lo[k] = d.rmin[k];
+    if (e == 0.0) {
+      if (g->cmin[k] != g->cmax[k]) return;   // cannot happen for points that share the coordinate; stay exact anyway
+      v.flat_mask |= 1 << k;
+      v.flat_val[k] = g->cmin[k];
+    } else { vol *= e; ++nd; }
+  }
+  if (nd == 0 || !(vol > 0.0) || !std::isfinite(vol)) return;
+  size_t free_b = 0, total_b = 0;
+  CU(cudaMemGetInfo(&free_b, &total_b));
+  double want = (double)d.n_cells * g->voxel_density / 100.0;
+  const double cap = std::min((double)free_b / 4.0, (double)total_b / 8.0) / (VOX_K * 4.0);
+  want = std::max(1.0, std::min(want, std::min(cap, 1.5e9)));
+  const double hv = std::pow(vol / want, 1.0 / nd);
+  int64_t n_vox = 1;
+  for (int k = 0; k < 3; ++k) {
+    if (v.flat_mask >> k & 1) { v.n[k] = 1; v.inv[k] = 0.0; v.h[k] = 0.0; continue; }
+    const double e = d.rmax[k] - d.rmin[k];
+    v.n[k] = (int)std::max(1.0, std::min(4096.0, std::ceil(e / hv)));
+    v.h[k] = e / v.n[k];
+    v.inv[k] = v.n[k] / e;
+    // the inflation of the voxel boxes (1e-3 h) must dwarf the rounding of lo + i*h at these coordinates
+    const double mag = std::max(std::fabs(d.rmin[k]), std::fabs(d.rmax[k]));
+    if (!(v.h[k] * 1e-3 > 1e4 * mag * 2.3e-16) || !std::isfinite(v.inv[k])) return;
+    n_vox *= v.n[k];
+  }
+  if ((double)n_vox > cap) return;
+  DevBuf<uint32_t> lists;
+  DevBuf<unsigned long long> st;
+  lists.alloc((size_t)n_vox * VOX_K);
+  st.alloc(2);
+  CU(cudaMemset(st.p, 0, 2 * sizeof(unsigned long long)));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  CU(cudaEventRecord(e0, nullptr));
+  g->n_launches += launch_build_voxels(d, v, n_vox, lists.p, st.p, nullptr);
+  CU(cudaEventRecord(e1, nullptr));
+  CU(cudaGetLastError());
+  CU(cudaDeviceSynchronize());
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  unsigned long long h[2];
+  CU(cudaMemcpy(h, st.p, sizeof(h), cudaMemcpyDeviceToHost));
+  g->vox_flagged = (int64_t)h[0];
+  g->vox_entries = (int64_t)h[1];
+  g->vox_build_ms = ms;
+  d.n_vox = n_vox;
+  d.vox_lists = lists.take();
+  v.lists = d.vox_lists;
+  d.vox = v;
+}
 
 int create_from_arrays(int cell_type, int n_points, int n_cells, const double* points, const int32_t* cells,
                        const int32_t* neighbors, int n_pd, const double* pd, int n_cd, const double* cd, int n_icd,
@@ -265,6 +343,13 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     std::vector<double> h_centers((size_t)3 * n_cells);
     CU(cudaMemcpyAsync(h_centers.data(), d_centers.p, h_centers.size() * 8, cudaMemcpyDeviceToHost, s));
     CU(cudaStreamSynchronize(s));
+    for (int k = 0; k < 3; ++k) g->cmin[k] = g->cmax[k] = h_centers[k];
+    for (size_t i = 1; i < (size_t)n_cells; ++i)
+      for (int k = 0; k < 3; ++k) {
+        const double v = h_centers[3 * i + k];
+        g->cmin[k] = v < g->cmin[k] ? v : g->cmin[k];
+        g->cmax[k] = v > g->cmax[k] ? v : g->cmax[k];
+      }
     KdTreeHost tree;
     build_kdtree(h_centers.data(), n_cells, tree);
     std::vector<double>().swap(h_centers);
@@ -276,6 +361,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     CU(cudaMalloc((void**)&d.orig_of_dev, n_slots * 4));
     CU(cudaMalloc((void**)&d.dev_of_orig, ((size_t)n_cells + 1) * 4));
     CU(cudaMalloc((void**)&d.centers4, n_slots * 24));
+    CU(cudaMalloc((void**)&d.cen32, n_slots * 32));
     CU(cudaMalloc((void**)&d.rec, n_slots * rec_stride(ppc) * 8));
     CU(cudaMalloc((void**)&d.counters, CNT_N * sizeof(unsigned long long)));
     CU(cudaMemsetAsync(d.counters, 0, CNT_N * sizeof(unsigned long long), s));
@@ -300,6 +386,9 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     CU(cudaMemcpyAsync(d.orig_of_dev, tree.orig_of_slot.data(), n_slots * 4, cudaMemcpyHostToDevice, s));
     g->n_launches += launch_build_records(d, d_points.p, d_cells.p, d_neigh.p, d_centers.p, s);
     CU(cudaStreamSynchronize(s));
+    d_points.release(); d_cells.release(); d_neigh.release(); d_centers.release();
+    if (const char* env = std::getenv("IU_B200_NN_VOXEL_DENSITY")) g->voxel_density = std::max(0, std::atoi(env));
+    build_voxel_table(g);
     // data tables
     d.n_pd = n_pd;
     d.pd_stride = round_up_stride(n_pd);
@@ -322,7 +411,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + tree.box.size() * sizeof(float) +
+    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + tree.box.size() * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));
@@ -637,6 +726,16 @@ int iu_b200_set_option(iu_b200_grid* g, int option, int64_t value) {
       if (value < 0 || value > 1) break;
       g->time_kernels = value != 0;
       return IU_B200_OK;
+    case IU_B200_OPT_NN_VOXEL_DENSITY: {
+      if (value < 0 || value > 6400) break;
+      std::lock_guard<std::mutex> lock(g->mu);
+      return guarded([&]() {
+        DeviceGuard guard(g->device);
+        g->voxel_density = (int)value;
+        build_voxel_table(g);
+        return IU_B200_OK;
+      });
+    }
     default:
       set_error("unknown option");
       return IU_B200_EINVAL;
@@ -656,7 +755,12 @@ int iu_b200_get_stats(const iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
     stats[IU_B200_STAT_WALK_LIMIT_HITS] = (int64_t)c[CNT_WALK_LIMIT];
     stats[IU_B200_STAT_QUERIES] = g->n_queries;
     stats[IU_B200_STAT_WORKSPACE_BYTES] = (int64_t)workspace_bytes(g);
-    stats[IU_B200_STAT_MESH_BYTES] = (int64_t)g->mesh_bytes;
+    stats[IU_B200_STAT_MESH_BYTES] = (int64_t)(g->mesh_bytes + (size_t)g->dg.n_vox * VOX_K * 4);
+    stats[IU_B200_STAT_NN_VOXELS] = g->dg.n_vox;
+    stats[IU_B200_STAT_NN_VOXELS_TREE] = g->vox_flagged;
+    stats[IU_B200_STAT_NN_VOXEL_ENTRIES] = g->vox_entries;
+    stats[IU_B200_STAT_NN_TREE_QUERIES] = (int64_t)c[CNT_NN_TREE];
+    stats[IU_B200_STAT_NN_VOXEL_BUILD_US] = (int64_t)(g->vox_build_ms * 1e3);
     stats[IU_B200_STAT_TREE_DEPTH] = g->tree_depth;
     stats[IU_B200_STAT_NOT_FOUND] = (int64_t)c[CNT_NOT_FOUND];
     collect_timings(const_cast<iu_b200_grid*>(g));
@@ -677,6 +781,7 @@ int iu_b200_reset_stats(iu_b200_grid* g) {
     CU(cudaMemcpy(c, g->dg.counters, sizeof(c), cudaMemcpyDeviceToHost));
     c[CNT_WALK_LIMIT] = 0;
     c[CNT_NOT_FOUND] = 0;
+    c[CNT_NN_TREE] = 0;
     c[CNT_EARLY] = 0;   // the hint-error counter is kept: iu_b200_check_dev compares it with `seen`
     CU(cudaMemcpy(g->dg.counters, c, sizeof(c), cudaMemcpyHostToDevice));
     for (int i = 0; i < CNT_N; ++i) g->seen[i] = c[i];

@@ -34,7 +34,24 @@ enum QueryMode : int {
 };
 
 // counters (device, unsigned long long each)
-enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_EARLY = 3, CNT_TICKET = 4, CNT_N = 5 };
+enum { CNT_HINT_ERROR = 0, CNT_WALK_LIMIT = 1, CNT_NOT_FOUND = 2, CNT_EARLY = 3, CNT_TICKET = 4, CNT_NN_TREE = 5, CNT_N = 6 };
+
+// Voxel table of the nearest-centre search (kernels.cu: k_build_voxels / nn_voxel).  A regular grid over the bounding box
+// of the points; every voxel owns VOX_K slot ids = a SUPERSET of all centres that are the nearest centre of some point of
+// the voxel (its Voronoi cells, found with the kd-tree at set-up).  A query inside the grid evaluates those candidates
+// with the exact fp64 distance of the tree's leaf scan; voxels with more than VOX_K candidates carry VOX_TREE and
+// queries outside the grid use the kd-tree.
+constexpr int VOX_K = 16;
+constexpr uint32_t VOX_END = 0xffffffffu, VOX_TREE = 0xfffffffeu;
+struct VoxelGrid {
+  const uint32_t* lists = nullptr;   // n_vox x VOX_K slot ids (groups of four; a group starting with VOX_END ends the list)
+  double lo[3] = {0, 0, 0};          // origin = rmin of the points
+  double inv[3] = {0, 0, 0};         // voxels per unit length (0 in flat dimensions)
+  double h[3] = {0, 0, 0};           // voxel size (0 in flat dimensions)
+  double flat_val[3] = {0, 0, 0};    // flat dimension: the coordinate every centre has there (queries must match it exactly)
+  int n[3] = {1, 1, 1};
+  int flat_mask = 0;                 // bit k: dimension k has zero extent
+};
 
 struct DeviceGrid {
   int cell_type = 0, ppc = 0, n_cells = 0, n_points = 0;
@@ -44,6 +61,10 @@ struct DeviceGrid {
   double* fat = nullptr;           // n_internal x {split, left child's split, right child's split, bits(3 x 2-bit dimension)}:
                                    // one 32-byte load decides two levels of a descent
   double* centers4 = nullptr;      // n_leaves x {x[LEAF], y[LEAF], z[LEAF]} (192-byte leaf blocks); padding slots = +inf
+  double* cen32 = nullptr;         // n_leaves*LEAF x {x, y, z, original id (low word)}: one 32-byte load per candidate
+  VoxelGrid vox;                   // lists == nullptr: no table, every cold query searches the tree
+  uint32_t* vox_lists = nullptr;   // owning pointer behind vox.lists
+  int64_t n_vox = 0;
   float* box = nullptr;            // (n_internal + n_leaves) x 8 floats: tight box of the centres below each node
   // mesh
   double* rec = nullptr;           // n_leaves*LEAF records
@@ -126,6 +147,9 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
                        uint32_t* idx, uint32_t* idx_alt, void* temp, size_t temp_bytes, int* end_bit_out,
                        cudaStream_t s);
 int morton_end_bit(const DeviceGrid& g);
+// fills lists (n_vox x VOX_K) for the grid described by v; stats[0] = voxels flagged VOX_TREE, stats[1] = sum of list lengths
+int launch_build_voxels(const DeviceGrid& g, const VoxelGrid& v, int64_t n_vox, uint32_t* lists, unsigned long long* stats,
+                        cudaStream_t s);
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s);
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s);
 int launch_ray_length_sample(int64_t n, int n_samples, const double* r0, const double* r1, double* sum, cudaStream_t s);

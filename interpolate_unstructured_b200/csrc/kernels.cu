@@ -164,16 +164,18 @@ template <int PPC, int CT>
 __global__ void k_build_records(int n_slots, const int32_t* __restrict__ orig_of_dev, const int32_t* __restrict__ dev_of_orig,
                                 const double* __restrict__ points, const int32_t* __restrict__ cells,
                                 const int32_t* __restrict__ neighbors, const double* __restrict__ centers,
-                                double* __restrict__ rec, double* __restrict__ centers4) {
+                                double* __restrict__ rec, double* __restrict__ centers4, double* __restrict__ cen32) {
   using L = RecLayout<PPC>;
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n_slots) return;
   const int o = orig_of_dev[s];
   double* R = rec + (size_t)s * L::STRIDE;
   double* C3 = centers4 + 24 * (size_t)(s / LEAF) + (s % LEAF);   // leaf block: x[8], y[8], z[8]
+  double* C4 = cen32 + 4 * (size_t)s;                             // {x, y, z, original id}
   if (o <= 0) {   // padding slot of the last leaf block: never the nearest, never visited
     const double inf = __longlong_as_double(0x7ff0000000000000LL);
     C3[0] = inf; C3[LEAF] = inf; C3[2 * LEAF] = inf;
+    C4[0] = inf; C4[1] = inf; C4[2] = inf; C4[3] = 0.0;
     for (int i = 0; i < L::STRIDE; ++i) R[i] = 0.0;
     return;
   }
@@ -223,6 +225,8 @@ __global__ void k_build_records(int n_slots, const int32_t* __restrict__ orig_of
   // leaf centre block entry; the centre is the array the tree was built from (bit-identical to
   // sum(cell_points)/ppc at :429)
   C3[0] = centers[3 * c]; C3[LEAF] = centers[3 * c + 1]; C3[2 * LEAF] = centers[3 * c + 2];
+  C4[0] = centers[3 * c]; C4[1] = centers[3 * c + 1]; C4[2] = centers[3 * c + 2];
+  C4[3] = __hiloint2double(0, o);
 }
 
 template <int PPC>
@@ -596,6 +600,192 @@ __device__ __forceinline__ int nearest_center(const TreeView& t, float* s_lb,
   return L.st.besti;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Voxel table of the nearest-centre search (device.h: VoxelGrid).
+//
+// k_build_voxels, one warp per voxel B (the voxel's box inflated by VOX_DELTA voxel sizes per side, which covers the
+// rounding of the query's voxel index): gathers with a depth-first traversal of the kd-tree every centre c with
+//     mindist^2(c, B) <= (1 + eps) * D2,   D2 = min over centres c' of maxdist^2(c', B)
+// (for q in B the nearest centre is at most maxdist(c', B) away), then drops every c for which some gathered c' has
+//     min over q in B of (|q - c|^2 - |q - c'|^2)  >  eps * maxdist^2(c, B)
+// (the difference is linear in q, so its minimum over the box sits at the corner picked per dimension by the sign of
+// c - c').  A dropped centre is, for every q of the voxel, farther than some other centre by a relative margin
+// eps = 1e-9, seven orders of magnitude above the rounding error of the fp64 distance the search computes, so the list
+// keeps every centre that can be nearest OR tie for nearest in computed arithmetic.  Voxels with more than VOX_K
+// survivors (or more than VOX_GATHER gathered) are flagged VOX_TREE.
+// ------------------------------------------------------------------------------------------------
+constexpr int VOX_GATHER = 128;
+constexpr double VOX_EPS = 1e-9, VOX_DELTA = 1e-3;
+
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, int64_t n_vox, uint32_t* __restrict__ lists,
+                                                      unsigned long long* __restrict__ stats) {
+  __shared__ double s_c[8][3][VOX_GATHER];
+  __shared__ int s_slot[8][VOX_GATHER];
+  __shared__ int s_stack[8][72];
+  __shared__ unsigned char s_alive[8][VOX_GATHER];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const double inf = __longlong_as_double(0x7ff0000000000000LL);
+  unsigned long long n_flagged = 0, n_entries = 0;
+  for (int64_t vox = (int64_t)blockIdx.x * 8 + w; vox < n_vox; vox += (int64_t)gridDim.x * 8) {
+    int iv[3];
+    iv[0] = (int)(vox % vg.n[0]); iv[1] = (int)((vox / vg.n[0]) % vg.n[1]); iv[2] = (int)(vox / ((int64_t)vg.n[0] * vg.n[1]));
+    double blo[3], bhi[3], bc[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (vg.flat_mask >> k & 1) { blo[k] = bhi[k] = bc[k] = vg.flat_val[k]; }
+      else {
+        blo[k] = vg.lo[k] + ((double)iv[k] - VOX_DELTA) * vg.h[k];
+        bhi[k] = vg.lo[k] + ((double)iv[k] + 1.0 + VOX_DELTA) * vg.h[k];
+        bc[k] = 0.5 * (blo[k] + bhi[k]);
+      }
+    }
+    double D2 = inf;
+    int count = 0, sp = 0;
+    bool overflow = false;
+    s_stack[w][sp++] = 0;
+    __syncwarp();
+    while (sp > 0) {
+      const int node = s_stack[w][--sp];
+      __syncwarp();
+      const float* b = t.box + 8 * (size_t)node;
+      double d2 = 0;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const double g = fmax(fmax((double)__ldg(b + k) - bhi[k], blo[k] - (double)__ldg(b + 3 + k)), 0.0);
+        d2 += g * g;
+      }
+      if (d2 > D2 * (1.0 + VOX_EPS)) continue;
+      if (node >= t.n_internal) {
+        const int base = (node - t.n_internal) * LEAF;
+        bool keep = false;
+        double cx = 0, cy = 0, cz = 0, maxd2 = inf;
+        if (lane < LEAF) {
+          const double* c = t.centers4 + 3 * (size_t)base + lane;
+          cx = __ldg(c); cy = __ldg(c + LEAF); cz = __ldg(c + 2 * LEAF);
+          if (cx < inf) {
+            const double ax = fmax(fabs(cx - blo[0]), fabs(cx - bhi[0])), ay = fmax(fabs(cy - blo[1]), fabs(cy - bhi[1])),
+                         az = fmax(fabs(cz - blo[2]), fabs(cz - bhi[2]));
+            maxd2 = (ax * ax + ay * ay) + az * az;
+            keep = true;
+          }
+        }
+        D2 = fmin(D2, warp_min(maxd2));
+        if (keep) {
+          const double gx = fmax(fmax(blo[0] - cx, cx - bhi[0]), 0.0), gy = fmax(fmax(blo[1] - cy, cy - bhi[1]), 0.0),
+                       gz = fmax(fmax(blo[2] - cz, cz - bhi[2]), 0.0);
+          keep = (gx * gx + gy * gy) + gz * gz <= D2 * (1.0 + VOX_EPS);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        const int pos = count + __popc(m & ((1u << lane) - 1u));
+        if (keep && pos < VOX_GATHER) { s_c[w][0][pos] = cx; s_c[w][1][pos] = cy; s_c[w][2][pos] = cz; s_slot[w][pos] = base + lane; }
+        count += __popc(m);
+        if (count > VOX_GATHER) { overflow = true; count = VOX_GATHER; }
+      } else {
+        const D4 f = ld256(t.fat + 4 * (size_t)node);
+        const int dim = __double2loint(f.w) & 3;
+        const int near = (dim == 0 ? bc[0] : dim == 1 ? bc[1] : bc[2]) < f.x ? 0 : 1;
+        if (lane == 0) { s_stack[w][sp] = 2 * node + 2 - near; s_stack[w][sp + 1] = 2 * node + 1 + near; }
+        sp += 2;
+        __syncwarp();
+      }
+    }
+    __syncwarp();
+    // survivors: within the final D2 and not dominated by any gathered centre
+    int n_alive = 0;
+    if (!overflow) {
+      for (int i = lane; i < count; i += 32) {
+        const double cx = s_c[w][0][i], cy = s_c[w][1][i], cz = s_c[w][2][i];
+        const double gx = fmax(fmax(blo[0] - cx, cx - bhi[0]), 0.0), gy = fmax(fmax(blo[1] - cy, cy - bhi[1]), 0.0),
+                     gz = fmax(fmax(blo[2] - cz, cz - bhi[2]), 0.0);
+        bool alive = (gx * gx + gy * gy) + gz * gz <= D2 * (1.0 + VOX_EPS);
+        const double ax = fmax(fabs(cx - blo[0]), fabs(cx - bhi[0])), ay = fmax(fabs(cy - blo[1]), fabs(cy - bhi[1])),
+                     az = fmax(fabs(cz - blo[2]), fabs(cz - bhi[2]));
+        const double margin = VOX_EPS * ((ax * ax + ay * ay) + az * az);
+        for (int j = 0; j < count && alive; ++j) {
+          const double ox = s_c[w][0][j], oy = s_c[w][1][j], oz = s_c[w][2][j];
+          const double qx = cx - ox > 0 ? bhi[0] : blo[0], qy = cy - oy > 0 ? bhi[1] : blo[1], qz = cz - oz > 0 ? bhi[2] : blo[2];
+          const double fi = ((qx - cx) * (qx - cx) + (qy - cy) * (qy - cy)) + (qz - cz) * (qz - cz);
+          const double fj = ((qx - ox) * (qx - ox) + (qy - oy) * (qy - oy)) + (qz - oz) * (qz - oz);
+          if (fi - fj > margin) alive = false;
+        }
+        s_alive[w][i] = alive ? 1 : 0;
+      }
+      __syncwarp();
+      // compact the survivors to the front (traversal order = nearest leaves first)
+      for (int i0 = 0; i0 < count; i0 += 32) {
+        const int i = i0 + lane;
+        const bool a = i < count && s_alive[w][i];
+        const int sl = i < count ? s_slot[w][i] : 0;
+        const unsigned m = __ballot_sync(0xffffffffu, a);
+        const int pos = n_alive + __popc(m & ((1u << lane) - 1u));
+        __syncwarp();
+        if (a && pos < VOX_K) s_slot[w][pos] = sl;   // pos <= i: only slots already read by this round are overwritten
+        n_alive += __popc(m);
+        __syncwarp();
+      }
+    }
+    const bool flagged = overflow || n_alive > VOX_K || n_alive == 0;
+    if (lane < VOX_K) {
+      uint32_t e;
+      if (flagged) e = lane == 0 ? VOX_TREE : VOX_END;
+      else if (lane < n_alive) e = (uint32_t)s_slot[w][lane];
+      else if (lane < ((n_alive + 3) & ~3)) e = (uint32_t)s_slot[w][n_alive - 1];   // pad the last group with a repeat
+      else e = VOX_END;
+      lists[(size_t)vox * VOX_K + lane] = e;
+    }
+    if (flagged) ++n_flagged; else n_entries += (unsigned long long)n_alive;
+    __syncwarp();
+  }
+  if (lane == 0) {
+    if (n_flagged) atomicAdd(stats, n_flagged);
+    if (n_entries) atomicAdd(stats + 1, n_entries);
+  }
+}
+
+// Nearest centre through the voxel table: the exact fp64 distance of scan_leaf for every listed candidate, ties to the
+// lowest original id.  Returns the 0-based device slot, or -2 when the query must search the tree (outside the grid,
+// NaN, off-plane query of a planar mesh, flagged voxel).
+__device__ __forceinline__ int nn_voxel(const VoxelGrid& V, const double* __restrict__ cen32, double qx, double qy, double qz) {
+  const double tx = (qx - V.lo[0]) * V.inv[0], ty = (qy - V.lo[1]) * V.inv[1], tz = (qz - V.lo[2]) * V.inv[2];
+  bool ok = tx >= 0.0 && tx < (double)V.n[0] && ty >= 0.0 && ty < (double)V.n[1] && tz >= 0.0 && tz < (double)V.n[2];
+  if (V.flat_mask) {
+    if ((V.flat_mask & 1) && qx != V.flat_val[0]) ok = false;
+    if ((V.flat_mask & 2) && qy != V.flat_val[1]) ok = false;
+    if ((V.flat_mask & 4) && qz != V.flat_val[2]) ok = false;
+  }
+  if (!ok) return -2;
+  const size_t vox = ((size_t)(int)tz * V.n[1] + (size_t)(int)ty) * V.n[0] + (size_t)(int)tx;
+  const uint4* L = reinterpret_cast<const uint4*>(V.lists) + vox * (VOX_K / 4);
+  double best = __longlong_as_double(0x7ff0000000000000LL);
+  int besti = -2, besto = 0x7fffffff;
+#pragma unroll 1
+  for (int g = 0; g < VOX_K / 4; ++g) {
+    const uint4 e = __ldg(L + g);
+    if (e.x >= VOX_TREE) break;   // VOX_END: list complete; VOX_TREE (first group only): besti stays -2
+    const uint32_t sl[4] = {e.x, e.y, e.z, e.w};
+    D4 c[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c[j] = ld256(cen32 + 4 * (size_t)sl[j]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const double dx = c[j].x - qx, dy = c[j].y - qy, dz = c[j].z - qz;
+      const double sd = (dx * dx + dy * dy) + dz * dz;
+      const int o = __double2loint(c[j].w);
+      const bool take = sd < best || (sd == best && o < besto);
+      best = take ? sd : best;
+      besti = take ? (int)sl[j] : besti;
+      besto = take ? o : besto;
+    }
+  }
+  return besti;
+}
+
 // iu_get_cell_through_neighbors (:667-725) + get_cell_intersection (:729-764).
 // Cells are 1-based DEVICE ids.  mask = icell_data column (original cell order) or null.
 template <int PPC>
@@ -732,6 +922,8 @@ template <> struct Weights<IU_QUAD_CT> {
 
 struct QueryKernelParams {
   TreeView tree;
+  VoxelGrid vox;
+  const double* cen32;
   const double* rec;
   const int32_t* dev_of_orig;
   const int32_t* orig_of_dev;
@@ -755,6 +947,17 @@ struct QueryKernelParams {
   int ivars[MAX_VARS];
 };
 
+// find_nearby_cell_kdtree (:272-288): the voxel table where it applies, else the kd-tree search
+__device__ __forceinline__ int nearest_slot(const QueryKernelParams& P, float* s_lb, double qx, double qy, double qz) {
+  int slot = -2;
+  if (P.vox.lists) slot = nn_voxel(P.vox, P.cen32, qx, qy, qz);
+  if (slot == -2) {
+    if (P.vox.lists) atomicAdd(P.counters + CNT_NN_TREE, 1ULL);
+    slot = nearest_center(P.tree, s_lb, qx, qy, qz);
+  }
+  return slot;
+}
+
 // Everything after the start cell is known: ray walk from the start cell's centre (iu_get_cell,
 // :429-432), then the mode's output.  `start` is a 1-based device id; for QM_INTERP_ICELL it is the
 // containing cell itself (no walk).
@@ -764,8 +967,8 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
   using L = RecLayout<PPC>;
   int ic = start;
   if (MODE != QM_INTERP_ICELL) {
-    const double* c3 = P.tree.centers4 + 24 * (size_t)((start - 1) / LEAF) + ((start - 1) % LEAF);
-    const V3 r0{__ldg(c3), __ldg(c3 + LEAF), __ldg(c3 + 2 * LEAF)};                   // :429
+    const D4 c0 = ld256(P.cen32 + 4 * (size_t)(start - 1));
+    const V3 r0{c0.x, c0.y, c0.z};                                                    // :429
     V3 r_p; int n_steps = 0, status; bool early;
     walk_ray<PPC>(P.rec, r0, V3{qx, qy, qz}, start, P.max_steps, nullptr, ic, r_p, n_steps, status, early);
     if (!early && n_steps > P.max_steps) {
@@ -910,7 +1113,7 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       }
     }
     if (MODE == QM_NEAREST) {
-      const int slot = nearest_center(P.tree, s_lb, qx, qy, qz);
+      const int slot = nearest_slot(P, s_lb, qx, qy, qz);
       ST_STREAM(P.out_i32 + i, slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0);
       continue;
     }
@@ -921,7 +1124,7 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       if (h < 1) { atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
       start = __ldg(P.dev_of_orig + h);
     } else if (h < 1) {                                                                // :422-423
-      const int slot = nearest_center(P.tree, s_lb, qx, qy, qz);
+      const int slot = nearest_slot(P, s_lb, qx, qy, qz);
       if (slot < 0) { ST_STREAM(P.i_cell + i, 0); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); continue; }
       start = slot + 1;
     } else {
@@ -1193,11 +1396,11 @@ int launch_build_records(const DeviceGrid& g, const double* points, const int32_
   const int b = blocks_for(n_slots, 128);
   k_fill_dev_of_orig<<<blocks_for(n_slots, 256), 256, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig);
   if (g.cell_type == IU_TRIANGLE_CT)
-    k_build_records<3, IU_TRIANGLE_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4);
+    k_build_records<3, IU_TRIANGLE_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4, g.cen32);
   else if (g.cell_type == IU_QUAD_CT)
-    k_build_records<4, IU_QUAD_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4);
+    k_build_records<4, IU_QUAD_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4, g.cen32);
   else
-    k_build_records<4, IU_TETRA_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4);
+    k_build_records<4, IU_TETRA_CT><<<b, 128, 0, s>>>(n_slots, g.orig_of_dev, g.dev_of_orig, points, cells, neighbors, centers, g.rec, g.centers4, g.cen32);
   return 2;
 }
 
@@ -1293,10 +1496,21 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
   return 1 + 2 + (end_bit + 7) / 8;
 }
 
+int launch_build_voxels(const DeviceGrid& g, const VoxelGrid& v, int64_t n_vox, uint32_t* lists, unsigned long long* stats,
+                        cudaStream_t s) {
+  if (n_vox == 0) return 0;
+  const TreeView t{g.fat, g.centers4, g.orig_of_dev, g.box, g.n_internal};
+  const int64_t need = (n_vox + 7) / 8;
+  const int b = (int)std::min<int64_t>(need, (int64_t)sm_count() * 8);
+  k_build_voxels<<<b, 256, 0, s>>>(t, v, n_vox, lists, stats);
+  return 1;
+}
+
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
   QueryKernelParams P;
   P.tree = TreeView{g.fat, g.centers4, g.orig_of_dev, g.box, g.n_internal};
+  P.vox = g.vox; P.cen32 = g.cen32;
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;

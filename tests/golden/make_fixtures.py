@@ -1,11 +1,15 @@
 #!/usr/bin/env python3
-"""Regenerates tests/golden/*.binda from the reference's VTU fixtures (/root/reference/test_data).
+"""Regenerates tests/golden/*.binda from the reference's VTU fixtures (/root/reference/test_data)
+by running the reference's own, UNMODIFIED converter /root/reference/convert_to_binary.py.
 
-Runs only in the build container (the reference tree does not exist on the GPU box); the
-resulting .binda files are committed.  It plays the role of ``convert_to_binary.py`` (which
-needs meshio, absent here): same entry order, dtypes and neighbour convention
-(convert_to_binary.py:118-162, :202-224).  dtypes follow the VTU arrays (Float32 stays float32,
-integers become int32).
+The converter needs ``meshio`` (absent on this image) only for ``meshio.read`` (:8, :185); a stub
+module of that name (written to a temp dir on sys.path) serves the mesh from the VTU parser below
+with meshio's attribute layout (points, cells[0].type/.data, point_data, cell_data).  BindaWriter
+(:11-115) and get_cell_neighbors (:118-162) are therefore the reference's code, and the committed
+.binda files are reference output.  Also writes neighbors_golden.json: sha256 of the reference's
+get_cell_neighbors on a 118k-tet jittered Kuhn mesh with duplicated points (tests/test_n1_reference.py).
+
+Runs only in the build container (the reference tree does not exist on the GPU box).
 """
 import os
 import re
@@ -56,13 +60,81 @@ def read_vtu(path):
     return points, conn, ctype, pdata, cdata
 
 
+MESHIO_STUB = '''"""Stand-in for meshio on an image without it: read() only, served by tests/golden/make_fixtures.read_vtu."""
+import importlib.util, os
+_spec = importlib.util.spec_from_file_location("_iu_make_fixtures", os.environ["IU_MAKE_FIXTURES"])
+_mf = importlib.util.module_from_spec(_spec)
+_spec.loader.exec_module(_mf)
+
+
+class CellBlock:
+    def __init__(self, type, data):
+        self.type, self.data = type, data
+
+
+class Mesh:
+    pass
+
+
+def read(filename):
+    points, conn, ctype, pdata, cdata = _mf.read_vtu(filename)
+    m = Mesh()
+    m.points = points
+    m.cells = [CellBlock(ctype, conn)]
+    m.point_data = dict(pdata)
+    m.cell_data = {k: [v] for k, v in cdata.items()}
+    return m
+'''
+
+CONVERTER = "/root/reference/convert_to_binary.py"
+
+
+def run_reference_converter(infile, out_basename):
+    """Executes the unmodified reference converter on `infile` (meshio stubbed) and returns its globals
+    (BindaWriter, get_cell_neighbors, ...)."""
+    import runpy
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        with open(os.path.join(td, "meshio.py"), "w") as f:
+            f.write(MESHIO_STUB)
+        os.environ["IU_MAKE_FIXTURES"] = os.path.abspath(__file__)
+        argv, path = sys.argv, list(sys.path)
+        sys.modules.pop("meshio", None)
+        sys.path.insert(0, td)
+        sys.argv = [CONVERTER, infile, "-output_basename", out_basename, "-force"]
+        try:
+            return runpy.run_path(CONVERTER, run_name="__main__")
+        finally:
+            sys.argv, sys.path[:] = argv, path
+            sys.modules.pop("meshio", None)
+
+
+def neighbor_case():
+    """118k-tet jittered Kuhn mesh whose points are all duplicated (every second cell refers to the copies)."""
+    pts, cells = meshgen.kuhn_tet_mesh(27, jitter=0.15, seed=99, shuffle=True)
+    npts = len(pts)
+    pts2 = np.concatenate([pts, pts])
+    cells2 = cells.copy()
+    cells2[1::2] += npts
+    return pts2, cells2
+
+
 def main():
+    import hashlib
+    import json
+    ref = None
     for name in ["triangle", "quad", "tetra", "tetra_cell", "tetra_two_cell"]:
-        points, conn, ctype, pdata, cdata = read_vtu(os.path.join(REF, name + ".vtu"))
-        neigh = meshgen.cell_neighbors(conn, points, ctype)
-        out = os.path.join(HERE, name + ".binda")
-        binda.write_grid_binda(out, points, conn, ctype, neigh, pdata, cdata)
-        print(name, ctype, points.shape, points.dtype, conn.shape, list(pdata), "boundary faces:", int((neigh < 0).sum()))
+        ref = run_reference_converter(os.path.join(REF, name + ".vtu"), os.path.join(HERE, name))
+        ents = binda.read_binda(os.path.join(HERE, name + ".binda"))
+        print(name, [(e.name, e.metadata, e.data.dtype.name, e.data.shape) for e in ents])
+    pts, cells = neighbor_case()
+    nb = ref["get_cell_neighbors"](cells, pts, 3)
+    digest = hashlib.sha256(np.ascontiguousarray(nb, dtype=np.int32).tobytes()).hexdigest()
+    with open(os.path.join(HERE, "neighbors_golden.json"), "w") as f:
+        json.dump({"case": "meshgen.kuhn_tet_mesh(27, jitter=0.15, seed=99, shuffle=True), points duplicated, odd cells on the copies",
+                   "n_cells": int(len(cells)), "n_points": int(len(pts)), "boundary_faces": int((nb < 0).sum()),
+                   "sha256_int32": digest, "source": "get_cell_neighbors of /root/reference/convert_to_binary.py:118-162"}, f, indent=1)
+    print("neighbors golden:", len(cells), "tets", digest)
 
 
 if __name__ == "__main__":
