@@ -133,6 +133,9 @@ int iu_b200_grid_bounds(const iu_b200_grid* grid, double rmin[3], double rmax[3]
 int iu_b200_get_point_data_index(const iu_b200_grid* grid, const char* name);
 int iu_b200_get_cell_data_index(const iu_b200_grid* grid, const char* name);
 int iu_b200_get_icell_data_index(const iu_b200_grid* grid, const char* name);
+/* Names of the columns of a grid built from arrays (iu_b200_grid_create has no name fields; iu_b200_grid_from_binda
+ * takes them from the file like :894-911): kind 0 point_data, 1 cell_data, 2 icell_data; i_var 1-based. */
+int iu_b200_set_data_name(iu_b200_grid* grid, int kind, int i_var, const char* name);
 /* name of a column (for iu_write_vtk-style consumers); NULL if out of range */
 const char* iu_b200_point_data_name(const iu_b200_grid* grid, int i_var);
 const char* iu_b200_cell_data_name(const iu_b200_grid* grid, int i_var);
@@ -160,7 +163,7 @@ int iu_b200_download_cell_data(iu_b200_grid* grid, int col0, int n_cols, double*
 int iu_b200_download_icell_data(iu_b200_grid* grid, int col0, int n_cols, int32_t* data);
 
 int iu_b200_set_option(iu_b200_grid* grid, int option, int64_t value);
-int iu_b200_get_stats(const iu_b200_grid* grid, int64_t stats[IU_B200_N_STATS]);
+int iu_b200_get_stats(iu_b200_grid* grid, int64_t stats[IU_B200_N_STATS]);
 int iu_b200_reset_stats(iu_b200_grid* grid);
 
 /* ---- the hot path, host buffers ------------------------------------------------------------ */
@@ -262,7 +265,8 @@ int iu_b200_export_geometry(iu_b200_grid* grid, double* cell_points, double* cel
                             double* cell_centers);
 
 /* The raw mesh back from the device records, ORIGINAL order: points (3, Np), cells (ppc, Nc)
- * 1-based.  Either pointer may be NULL.  Points no cell refers to come back as zeros. */
+ * 1-based.  Either pointer may be NULL.  points is the array the grid was created from (ug%points), so points
+ * that no cell refers to are kept. */
 int iu_b200_export_mesh(iu_b200_grid* grid, double* points, int32_t* cells);
 
 /* iu_write_vtk(ug, filename) (m_interp_unstructured.f90:930-985 through m_vtk.f90:45-221): the

@@ -69,6 +69,7 @@ _SIGNATURES = {
     "iu_b200_get_point_data_index": (C.c_int, [c_vp, C.c_char_p]),
     "iu_b200_get_cell_data_index": (C.c_int, [c_vp, C.c_char_p]),
     "iu_b200_get_icell_data_index": (C.c_int, [c_vp, C.c_char_p]),
+    "iu_b200_set_data_name": (C.c_int, [c_vp, C.c_int, C.c_int, C.c_char_p]),
     "iu_b200_point_data_name": (C.c_char_p, [c_vp, C.c_int]),
     "iu_b200_cell_data_name": (C.c_char_p, [c_vp, C.c_int]),
     "iu_b200_icell_data_name": (C.c_char_p, [c_vp, C.c_int]),
@@ -270,7 +271,7 @@ class Grid:
 
     @classmethod
     def from_arrays(cls, cell_type, points, cells0, neighbors0, point_data=None, cell_data=None, icell_data=None,
-                    point_names=None, device=-1):
+                    point_names=None, cell_names=None, icell_names=None, device=-1):
         """cells0 / neighbors0 are 0-based as on disk (+1 applied here like :871-872); data tables
         are (n_rows, n_columns)."""
         ct = CELL_TYPES.get(cell_type, cell_type)
@@ -298,7 +299,14 @@ class Grid:
                   neigh.ctypes.data_as(c_ip), npd, pd_p, ncd, cd_p, nicd, icd_p, int(device))
         h = c_vp()
         _check(lib().iu_b200_grid_create(C.byref(d), C.byref(h)))
-        return cls(h.value)
+        g = cls(h.value)
+        for kind, names, n in ((0, point_names, npd), (1, cell_names, ncd), (2, icell_names, nicd)):
+            if names is not None:
+                if len(names) != n:
+                    raise ValueError("one name per data column expected")
+                for i, nm in enumerate(names):
+                    _check(lib().iu_b200_set_data_name(g._h, kind, i + 1, str(nm).encode()))
+        return g
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:

@@ -123,6 +123,11 @@ struct iu_b200_grid {
   double timed_ns[2] = {0, 0};
   int64_t timed_launches[2] = {0, 0};
   std::mutex mu;   // one batch call at a time per grid (workspaces are per grid)
+  // The sort buffers, the ticket counter and the tracer workspace are per grid: a call enqueued on another stream
+  // than the previous one first waits (on the device) for that call's last kernel.
+  cudaEvent_t ws_done = nullptr;
+  cudaStream_t ws_stream = nullptr;
+  bool ws_used = false;
 };
 
 namespace {
@@ -153,6 +158,20 @@ cudaEvent_t timing_event(iu_b200_grid* g) {
   return e;
 }
 
+// Brackets every use of the per-grid device workspace on stream s (run_query / run_walk / run_trace).
+struct WorkspaceScope {
+  iu_b200_grid* g; cudaStream_t s;
+  WorkspaceScope(iu_b200_grid* g_, cudaStream_t s_) : g(g_), s(s_) {
+    if (!g->ws_done) CU(cudaEventCreateWithFlags(&g->ws_done, cudaEventDisableTiming));
+    if (g->ws_used && g->ws_stream != s) CU(cudaStreamWaitEvent(s, g->ws_done, 0));
+  }
+  ~WorkspaceScope() {
+    cudaEventRecord(g->ws_done, s);
+    g->ws_stream = s;
+    g->ws_used = true;
+  }
+};
+
 // kind 0 = hot query kernel, 1 = Morton keys + radix sort
 struct TimedScope {
   iu_b200_grid* g; cudaStream_t s; int kind; cudaEvent_t a = nullptr;
@@ -182,7 +201,7 @@ void collect_timings(iu_b200_grid* g) {
 }
 
 void free_device_grid(DeviceGrid& d) {
-  cudaFree(d.cen32); cudaFree(d.vox_lists);
+  cudaFree(d.cen32); cudaFree(d.vox_lists); cudaFree(d.points);
   cudaFree(d.fat); cudaFree(d.box); cudaFree(d.centers4); cudaFree(d.rec); cudaFree(d.dev_of_orig);
   cudaFree(d.orig_of_dev); cudaFree(d.pd); cudaFree(d.cd); cudaFree(d.icd); cudaFree(d.counters);
   d = DeviceGrid();
@@ -386,7 +405,8 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     CU(cudaMemcpyAsync(d.orig_of_dev, tree.orig_of_slot.data(), n_slots * 4, cudaMemcpyHostToDevice, s));
     g->n_launches += launch_build_records(d, d_points.p, d_cells.p, d_neigh.p, d_centers.p, s);
     CU(cudaStreamSynchronize(s));
-    d_points.release(); d_cells.release(); d_neigh.release(); d_centers.release();
+    d.points = d_points.take();
+    d_cells.release(); d_neigh.release(); d_centers.release();
     if (const char* env = std::getenv("IU_B200_NN_VOXEL_DENSITY")) g->voxel_density = std::max(0, std::atoi(env));
     build_voxel_table(g);
     // data tables
@@ -411,7 +431,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = n_slots * (rec_stride(ppc) * 8 + 24 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + tree.box.size() * sizeof(float) +
+    g->mesh_bytes = (size_t)n_points * 24 + n_slots * (rec_stride(ppc) * 8 + 24 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + tree.box.size() * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));
@@ -486,6 +506,7 @@ int iu_b200_grid_destroy(iu_b200_grid* g) {
     g->tr_seed.release(); g->tr_field.release(); g->tr_cell.release(); g->walk_sum.release();
     if (g->h_walk_sum) cudaFreeHost(g->h_walk_sum);
     if (g->walk_ev) cudaEventDestroy(g->walk_ev);
+    if (g->ws_done) cudaEventDestroy(g->ws_done);
     if (g->s_in) cudaStreamDestroy(g->s_in);
     if (g->s_comp) cudaStreamDestroy(g->s_comp);
     if (g->s_out) cudaStreamDestroy(g->s_out);
@@ -520,6 +541,14 @@ static int find_name(const std::vector<std::string>& names, const char* name) {
 int iu_b200_get_point_data_index(const iu_b200_grid* g, const char* name) { return g ? find_name(g->point_names, name) : -1; }
 int iu_b200_get_cell_data_index(const iu_b200_grid* g, const char* name) { return g ? find_name(g->cell_names, name) : -1; }
 int iu_b200_get_icell_data_index(const iu_b200_grid* g, const char* name) { return g ? find_name(g->icell_names, name) : -1; }
+int iu_b200_set_data_name(iu_b200_grid* g, int kind, int i_var, const char* name) {
+  if (!g || !name || kind < 0 || kind > 2) { set_error("bad argument"); return IU_B200_EINVAL; }
+  std::lock_guard<std::mutex> lock(g->mu);
+  std::vector<std::string>& names = kind == 0 ? g->point_names : kind == 1 ? g->cell_names : g->icell_names;
+  if (i_var < 1 || i_var > (int)names.size()) { set_error("column outside 1..n"); return IU_B200_EINVAL; }
+  names[i_var - 1] = name;
+  return IU_B200_OK;
+}
 const char* iu_b200_point_data_name(const iu_b200_grid* g, int i_var) {
   if (!g || i_var < 1 || i_var > (int)g->point_names.size()) return nullptr;
   return g->point_names[i_var - 1].c_str();
@@ -744,9 +773,10 @@ int iu_b200_set_option(iu_b200_grid* g, int option, int64_t value) {
   return IU_B200_EINVAL;
 }
 
-int iu_b200_get_stats(const iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
+int iu_b200_get_stats(iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
   if (!g || !stats) { set_error("null argument"); return IU_B200_EINVAL; }
   for (int i = 0; i < IU_B200_N_STATS; ++i) stats[i] = 0;
+  std::lock_guard<std::mutex> lock(g->mu);
   return guarded([&]() {
     DeviceGuard guard(g->device);
     unsigned long long c[CNT_N];
@@ -763,7 +793,7 @@ int iu_b200_get_stats(const iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
     stats[IU_B200_STAT_NN_VOXEL_BUILD_US] = (int64_t)(g->vox_build_ms * 1e3);
     stats[IU_B200_STAT_TREE_DEPTH] = g->tree_depth;
     stats[IU_B200_STAT_NOT_FOUND] = (int64_t)c[CNT_NOT_FOUND];
-    collect_timings(const_cast<iu_b200_grid*>(g));
+    collect_timings(g);
     stats[IU_B200_STAT_QUERY_KERNEL_NS] = (int64_t)g->timed_ns[0];
     stats[IU_B200_STAT_QUERY_KERNEL_LAUNCHES] = g->timed_launches[0];
     stats[IU_B200_STAT_SORT_NS] = (int64_t)g->timed_ns[1];
@@ -811,6 +841,7 @@ bool want_sort(const iu_b200_grid* g, int mode, int64_t m) {
 // Runs one logical batch as sub-batches of at most dev_batch queries; each sub-batch is optionally
 // Morton-sorted (key, index) and processed through the permutation.
 void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
+  WorkspaceScope ws(g, s);
   const int64_t n = a.n;
   const int64_t step = g->dev_batch;
   const size_t out_row = a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL ? (size_t)a.n_vars : 1;
@@ -848,11 +879,15 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
 // IU_B200_OPT_SORT_QUERIES = 1 are they processed in Morton order of the start positions: measured on
 // C4 (100M rays), the 13 scattered accesses per ray through the permutation cost more than the
 // locality gains below ~2 cells per ray (18.5 -> 29.7 ms at 0.1 h) and pay off above (71 -> 32.6 ms at 1 h).
+// huge(1) (what the reference's own callers pass, :431, :1122) would overflow the do-loop counter on a walk that never
+// terminates (n_steps = max_steps + 1 after the loop): the cap keeps that sum representable
+constexpr int MAX_STEPS_CAP = 0x7ffffffe;
 constexpr int64_t WALK_AUTO_MIN_RAYS = 1 << 20;
 constexpr int WALK_AUTO_SAMPLES = 4096;
 constexpr double WALK_AUTO_CELLS = 0.55;
 
 void run_walk(iu_b200_grid* g, WalkArgs a, cudaStream_t s) {
+  WorkspaceScope ws(g, s);
   const int64_t n = a.n;
   const int64_t step = g->dev_batch;
   // auto: sorting pays once the rays cross more than about one cell (profiles/README.md, C4 table: unsorted
@@ -999,7 +1034,7 @@ int iu_b200_get_cell_through_neighbors_batch_dev(iu_b200_grid* g, int64_t n, int
   return guarded([&]() {
     DeviceGuard guard(g->device);
     WalkArgs a;
-    a.n = n; a.max_steps = max_steps; a.r0 = r0; a.r1 = r1; a.ic0 = ic0; a.ic1 = ic1; a.r_p = r_p;
+    a.n = n; a.max_steps = std::min(max_steps, MAX_STEPS_CAP); a.r0 = r0; a.r1 = r1; a.ic0 = ic0; a.ic1 = ic1; a.r_p = r_p;
     a.n_steps = n_steps; a.status = status; a.mask_col = i_icell_mask - 1;
     run_walk(g, a, (cudaStream_t)stream);
     return IU_B200_OK;
@@ -1064,12 +1099,11 @@ int iu_b200_export_mesh(iu_b200_grid* g, double* points, int32_t* cells) {
     DeviceGuard guard(g->device);
     DevBuf<double> p;
     DevBuf<int32_t> c;
-    if (points) { p.alloc((size_t)3 * g->dg.n_points); CU(cudaMemset(p.p, 0, p.n * 8)); }
     if (cells) c.alloc((size_t)g->dg.ppc * g->dg.n_cells);
     CU(cudaDeviceSynchronize());
-    g->n_launches += launch_export_mesh(g->dg, p.p, c.p, nullptr);
+    if (cells) g->n_launches += launch_export_mesh(g->dg, nullptr, c.p, nullptr);
     CU(cudaDeviceSynchronize());
-    if (points) CU(cudaMemcpy(points, p.p, p.n * 8, cudaMemcpyDeviceToHost));
+    if (points) CU(cudaMemcpy(points, g->dg.points, (size_t)3 * g->dg.n_points * 8, cudaMemcpyDeviceToHost));
     if (cells) CU(cudaMemcpy(cells, c.p, c.n * 4, cudaMemcpyDeviceToHost));
     return IU_B200_OK;
   });
@@ -1167,6 +1201,7 @@ int trace_args_ok(const iu_b200_grid* g, int64_t n, int ndim, int nvar, int inte
 void run_trace(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field, double min_dx, double max_dx,
                int max_steps, double rtol, double atol, int reverse, double* y, double* y_field, int32_t* n_steps,
                int axisymmetric, int i_icell_mask, int mask_value, int32_t* boundary_material, cudaStream_t s) {
+  WorkspaceScope ws(g, s);
   g->tr_seed.ensure((size_t)3 * n);
   g->tr_field.ensure((size_t)ndim * n);
   g->tr_cell.ensure((size_t)n);
@@ -1413,7 +1448,7 @@ int iu_b200_get_cell_through_neighbors_batch(iu_b200_grid* g, int64_t n, int max
     };
     auto compute = [&](Slot& sl, int64_t m) {
       WalkArgs a;
-      a.n = m; a.max_steps = max_steps; a.r0 = sl.r.p; a.r1 = sl.r1.p; a.ic0 = sl.i_a.p; a.ic1 = sl.i_b.p;
+      a.n = m; a.max_steps = std::min(max_steps, MAX_STEPS_CAP); a.r0 = sl.r.p; a.r1 = sl.r1.p; a.ic0 = sl.i_a.p; a.ic1 = sl.i_b.p;
       a.r_p = sl.out_f64.p; a.n_steps = sl.i_c.p; a.status = sl.i_d.p; a.mask_col = i_icell_mask - 1;
       a.mark_early = true;
       run_walk(g, a, g->s_comp);

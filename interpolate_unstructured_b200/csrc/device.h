@@ -68,6 +68,7 @@ struct DeviceGrid {
   float* box = nullptr;            // (n_internal + n_leaves) x 8 floats: tight box of the centres below each node
   // mesh
   double* rec = nullptr;           // n_leaves*LEAF records
+  double* points = nullptr;        // (3, n_points) as given: iu_write_vtk writes ug%points, including points no cell uses
   int32_t* dev_of_orig = nullptr;  // [n_cells + 1], index = 1-based original id -> 1-based device id
   int32_t* orig_of_dev = nullptr;  // [n_leaves*LEAF], 1-based original id, 0 = padding
   // data tables
