@@ -193,6 +193,17 @@ int iu_b200_get_cell_scalar_at_batch(iu_b200_grid* grid, int64_t n, const double
 int iu_b200_get_icell_scalar_at_batch(iu_b200_grid* grid, int64_t n, const double* r, int i_var, int32_t* i_guess,
                                       int32_t* res);
 
+/* iu_interpolate_at (:480-495) followed by iu_get_cell_scalar_at (:437-448) with the cell just found as i_guess, for n
+ * points in ONE pass over the queries (the composition BASELINE config C5 times: "8 point-data vars + cell data").
+ * Results are those of the two calls in sequence: var_at_r (n_vars, n) from the first call's cell; the second call
+ * walks again from that cell's centre (:424-432), writes cell_res[i] = cell_data(i_cell, i_cell_var) and leaves the
+ * cell it ended in in i_cell[i].  Rows of queries that were not found stay untouched.
+ * (Host-buffer form only: when the second walk of a found query leaves the domain - a query within rounding of a
+ * boundary face - its var_at_r row is left untouched as well; the device form writes it.) */
+int iu_b200_interpolate_and_cell_scalar_at_batch(iu_b200_grid* grid, int64_t n, const double* r, int n_vars,
+                                                 const int32_t* i_vars, int i_cell_var, double* var_at_r,
+                                                 double* cell_res, int32_t* i_cell);
+
 /* iu_get_cell_through_neighbors (:667-725) for n rays r0 -> r1 starting in cells ic0.
  * Outputs ic1, r_p (3, n), n_steps, status (0 reached, -1 left domain, 1 mask changed).
  * i_icell_mask = 0 means the optional argument is absent.  As in the reference, r_p and n_steps
@@ -233,6 +244,9 @@ int iu_b200_interpolate_at_batch_dev(iu_b200_grid* grid, int64_t n, const double
 int iu_b200_interpolate_at_icell_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int n_vars,
                                            const int32_t* i_vars /* host */, double* var_at_r,
                                            const int32_t* i_cell, void* stream);
+int iu_b200_interpolate_and_cell_scalar_at_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int n_vars,
+                                                     const int32_t* i_vars /* host */, int i_cell_var, double* var_at_r,
+                                                     double* cell_res, int32_t* i_cell, void* stream);
 int iu_b200_get_cell_scalar_at_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int i_var,
                                          int32_t* i_guess, double* res, void* stream);
 int iu_b200_get_icell_scalar_at_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int i_var,

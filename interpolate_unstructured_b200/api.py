@@ -90,6 +90,7 @@ _SIGNATURES = {
     "iu_b200_interpolate_at_batch": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, c_vp, c_vp]),
     "iu_b200_interpolate_scalar_at_batch": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp]),
     "iu_b200_interpolate_at_icell_batch": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, c_vp, c_vp]),
+    "iu_b200_interpolate_and_cell_scalar_at_batch": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, C.c_int, c_vp, c_vp, c_vp]),
     "iu_b200_get_cell_scalar_at_batch": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp]),
     "iu_b200_get_icell_scalar_at_batch": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp]),
     "iu_b200_get_cell_through_neighbors_batch": (C.c_int, [c_vp, C.c_int64, C.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int]),
@@ -97,6 +98,7 @@ _SIGNATURES = {
     "iu_b200_get_cell_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, c_vp, c_vp]),
     "iu_b200_interpolate_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, c_vp, c_vp, c_vp]),
     "iu_b200_interpolate_at_icell_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, c_vp, c_vp, c_vp]),
+    "iu_b200_interpolate_and_cell_scalar_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, C.c_int, c_vp, c_vp, c_vp, c_vp]),
     "iu_b200_get_cell_scalar_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp, c_vp]),
     "iu_b200_get_icell_scalar_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp, c_vp]),
     "iu_b200_get_cell_through_neighbors_batch_dev": (C.c_int, [c_vp, C.c_int64, C.c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, C.c_int, c_vp]),
@@ -484,6 +486,21 @@ class Grid:
         _check(lib().iu_b200_interpolate_at_icell_batch(self._h, n, _p(r), len(iv), iv.ctypes.data_as(c_ip), _p(var_at_r), _p(ic)))
         return var_at_r
 
+    def iu_interpolate_and_cell_scalar_at(self, r, i_vars, i_cell_var, var_at_r=None, cell_res=None, i_cell=None):
+        """iu_interpolate_at (:480-495) then iu_get_cell_scalar_at (:437-448) with the found cell as i_guess, in one pass
+        -> (var_at_r (n, n_vars), cell_res (n,), i_cell)."""
+        r, n, i_cell = self._prep(r, i_cell)
+        iv = np.ascontiguousarray(i_vars, dtype=np.int32).reshape(-1)
+        if var_at_r is None:
+            var_at_r = np.zeros((n, len(iv)))
+        if cell_res is None:
+            cell_res = np.zeros(n)
+        _inout(var_at_r, np.float64, (n, len(iv)), "var_at_r")
+        _inout(cell_res, np.float64, (n,), "cell_res")
+        _check(lib().iu_b200_interpolate_and_cell_scalar_at_batch(self._h, n, _p(r), len(iv), iv.ctypes.data_as(c_ip), int(i_cell_var),
+                                                                  _p(var_at_r), _p(cell_res), _p(i_cell)))
+        return var_at_r, cell_res, i_cell
+
     def iu_get_cell_scalar_at(self, r, i_var, i_guess=None, res=None):
         """iu_get_cell_scalar_at (:437-448) -> (res, i_guess)."""
         r, n, i_guess = self._prep(r, i_guess)
@@ -574,6 +591,14 @@ class Grid:
                                                             iv.ctypes.data_as(c_ip),
                                                             _dev_ptr(var_at_r, "float64", n * len(iv), "var_at_r"),
                                                             _dev_ptr(i_cell, "int32", n, "i_cell"), _cur_stream(self.device)))
+
+    def iu_interpolate_and_cell_scalar_at_dev(self, r, i_vars, i_cell_var, var_at_r, cell_res, i_cell):
+        n = i_cell.numel()
+        iv = np.ascontiguousarray(i_vars, dtype=np.int32).reshape(-1)
+        _check(lib().iu_b200_interpolate_and_cell_scalar_at_batch_dev(
+            self._h, n, _dev_ptr(r, "float64", 3 * n, "r"), len(iv), iv.ctypes.data_as(c_ip), int(i_cell_var),
+            _dev_ptr(var_at_r, "float64", n * len(iv), "var_at_r"), _dev_ptr(cell_res, "float64", n, "cell_res"),
+            _dev_ptr(i_cell, "int32", n, "i_cell"), _cur_stream(self.device)))
 
     def iu_get_cell_scalar_at_dev(self, r, i_var, i_guess, res):
         n = i_guess.numel()

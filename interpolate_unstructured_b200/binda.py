@@ -7,7 +7,7 @@ int64 n_entries, int64 total_header_size, then per entry a 464-byte record (128 
 offset), then the payloads in C order.  Integer arrays are stored as int32
 (convert_to_binary.py:48-49).
 
-The C++ reader inside libiu_b200.so (csrc/binda_io.cpp) is the product's reader; this module
+The C++ reader inside libiu_b200.so (csrc/host_mesh.cpp: read_binda_mesh) is the product's reader; this module
 is the Python-side writer used to produce grid files (the role convert_to_binary.py plays for
 the reference) plus a small reader for round-trip checks.
 """

@@ -844,7 +844,7 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
   WorkspaceScope ws(g, s);
   const int64_t n = a.n;
   const int64_t step = g->dev_batch;
-  const size_t out_row = a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL ? (size_t)a.n_vars : 1;
+  const size_t out_row = a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL || a.mode == QM_INTERP_CELL ? (size_t)a.n_vars : 1;
   for (int64_t off = 0; off < n; off += step) {
     const int64_t m = std::min(step, n - off);
     QueryArgs b = a;
@@ -853,6 +853,7 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
     b.i_cell = a.i_cell ? a.i_cell + off : nullptr;
     b.out_f64 = a.out_f64 ? a.out_f64 + out_row * off : nullptr;
     b.out_i32 = a.out_i32 ? a.out_i32 + off : nullptr;
+    b.out2_f64 = a.out2_f64 ? a.out2_f64 + off : nullptr;
     b.perm = nullptr;
     if (g->sort_mode == 3) {   // the caller's queries are already spatially ordered: ticket tiles without a permutation
       b.dynamic = g->dynamic_tiles;
@@ -950,10 +951,11 @@ int check_query_args(const iu_b200_grid* g, int64_t n, const void* r, int mode, 
   if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
   if (n < 0) { set_error("negative query count"); return IU_B200_EINVAL; }
   if (n > 0 && !r) { set_error("null query array"); return IU_B200_EINVAL; }
-  if (mode == QM_INTERP || mode == QM_INTERP_ICELL) {
+  if (mode == QM_INTERP || mode == QM_INTERP_ICELL || mode == QM_INTERP_CELL) {
     if (n_vars < 1 || n_vars > MAX_VARS || !i_vars) { set_error("n_vars must be in 1..32"); return IU_B200_EINVAL; }
     for (int v = 0; v < n_vars; ++v)
       if (i_vars[v] < 1 || i_vars[v] > g->dg.n_pd) { set_error("i_vars: column outside 1..n_point_data"); return IU_B200_EINVAL; }
+    if (mode == QM_INTERP_CELL && (i_var < 1 || i_var > g->dg.n_cd)) { set_error("i_var outside 1..n_cell_data"); return IU_B200_EINVAL; }
   } else if (mode == QM_CELL_F64) {
     if (i_var < 1 || i_var > g->dg.n_cd) { set_error("i_var outside 1..n_cell_data"); return IU_B200_EINVAL; }
   } else if (mode == QM_CELL_I32) {
@@ -963,13 +965,14 @@ int check_query_args(const iu_b200_grid* g, int64_t n, const void* r, int mode, 
 }
 
 QueryArgs make_args(const iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
-                    int32_t* i_cell, double* out_f64, int32_t* out_i32) {
+                    int32_t* i_cell, double* out_f64, int32_t* out_i32, double* out2_f64 = nullptr) {
   QueryArgs a;
-  a.mode = mode; a.n = n; a.r = r; a.i_cell = i_cell; a.out_f64 = out_f64; a.out_i32 = out_i32;
+  a.mode = mode; a.n = n; a.r = r; a.i_cell = i_cell; a.out_f64 = out_f64; a.out_i32 = out_i32; a.out2_f64 = out2_f64;
   a.max_steps = (int)g->max_walk_steps;
-  if (mode == QM_INTERP || mode == QM_INTERP_ICELL) {
+  if (mode == QM_INTERP || mode == QM_INTERP_ICELL || mode == QM_INTERP_CELL) {
     a.n_vars = n_vars;
     for (int v = 0; v < n_vars; ++v) a.ivars[v] = i_vars[v] - 1;
+    if (mode == QM_INTERP_CELL) a.cell_var = i_var - 1;
   } else if (mode == QM_CELL_F64 || mode == QM_CELL_I32) {
     a.n_vars = 1;
     a.ivars[0] = i_var - 1;
@@ -978,13 +981,13 @@ QueryArgs make_args(const iu_b200_grid* g, int mode, int64_t n, const double* r,
 }
 
 int query_dev(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
-              int32_t* i_cell, double* out_f64, int32_t* out_i32, void* stream) {
+              int32_t* i_cell, double* out_f64, int32_t* out_i32, void* stream, double* out2_f64 = nullptr) {
   int rc = check_query_args(g, n, r, mode, n_vars, i_vars, i_var);
   if (rc != IU_B200_OK || n == 0) return rc;
   std::lock_guard<std::mutex> lock(g->mu);
   return guarded([&]() {
     DeviceGuard guard(g->device);
-    run_query(g, make_args(g, mode, n, r, n_vars, i_vars, i_var, i_cell, out_f64, out_i32), (cudaStream_t)stream);
+    run_query(g, make_args(g, mode, n, r, n_vars, i_vars, i_var, i_cell, out_f64, out_i32, out2_f64), (cudaStream_t)stream);
     return IU_B200_OK;
   });
 }
@@ -1015,6 +1018,12 @@ int iu_b200_interpolate_at_batch_dev(iu_b200_grid* g, int64_t n, const double* r
 int iu_b200_interpolate_at_icell_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
                                            double* var_at_r, const int32_t* i_cell, void* stream) {
   return query_dev(g, QM_INTERP_ICELL, n, r, n_vars, i_vars, 0, const_cast<int32_t*>(i_cell), var_at_r, nullptr, stream);
+}
+int iu_b200_interpolate_and_cell_scalar_at_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int n_vars,
+                                                     const int32_t* i_vars, int i_cell_var, double* var_at_r, double* cell_res,
+                                                     int32_t* i_cell, void* stream) {
+  if (n > 0 && (!var_at_r || !cell_res || !i_cell)) { set_error("null output array"); return IU_B200_EINVAL; }
+  return query_dev(g, QM_INTERP_CELL, n, r, n_vars, i_vars, i_cell_var, i_cell, var_at_r, nullptr, stream, cell_res);
 }
 int iu_b200_get_cell_scalar_at_batch_dev(iu_b200_grid* g, int64_t n, const double* r, int i_var, int32_t* i_guess,
                                          double* res, void* stream) {
@@ -1350,14 +1359,15 @@ int run_pipeline(iu_b200_grid* g, int64_t n, int trigger, H2D&& h2d, COMPUTE&& c
 }
 
 int query_host(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
-               int32_t* i_cell, double* out_f64, int32_t* out_i32) {
+               int32_t* i_cell, double* out_f64, int32_t* out_i32, double* out2_f64 = nullptr) {
   int rc = check_query_args(g, n, r, mode, n_vars, i_vars, i_var);
   if (rc != IU_B200_OK || n == 0) return rc;
   if (mode != QM_NEAREST && !i_cell) { set_error("null i_cell array"); return IU_B200_EINVAL; }
-  const bool f64_out = mode == QM_INTERP || mode == QM_INTERP_ICELL || mode == QM_CELL_F64;
+  const bool fused = mode == QM_INTERP_CELL;
+  const bool f64_out = mode == QM_INTERP || mode == QM_INTERP_ICELL || mode == QM_CELL_F64 || fused;
   const bool i32_out = mode == QM_NEAREST || mode == QM_CELL_I32;
-  if ((f64_out && !out_f64) || (i32_out && !out_i32)) { set_error("null output array"); return IU_B200_EINVAL; }
-  const size_t row = mode == QM_INTERP || mode == QM_INTERP_ICELL ? (size_t)n_vars : 1;   // output words per query
+  if ((f64_out && !out_f64) || (i32_out && !out_i32) || (fused && !out2_f64)) { set_error("null output array"); return IU_B200_EINVAL; }
+  const size_t row = mode == QM_INTERP || mode == QM_INTERP_ICELL || fused ? (size_t)n_vars : 1;   // output words per query
   std::lock_guard<std::mutex> lock(g->mu);
   return guarded([&]() {
     DeviceGuard guard(g->device);
@@ -1367,13 +1377,14 @@ int query_host(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars
       if (mode != QM_NEAREST) sl.i_a.ensure(cap);
       if (f64_out) sl.out_f64.ensure(row * cap);
       if (i32_out) sl.i_b.ensure(cap);
+      if (fused) sl.r1.ensure(cap);
     }
     auto h2d = [&](Slot& sl, int64_t off, int64_t m) {
       CU(cudaMemcpyAsync(sl.r.p, r + 3 * off, (size_t)m * 24, cudaMemcpyHostToDevice, g->s_in));
       if (mode != QM_NEAREST) CU(cudaMemcpyAsync(sl.i_a.p, i_cell + off, (size_t)m * 4, cudaMemcpyHostToDevice, g->s_in));
     };
     auto compute = [&](Slot& sl, int64_t m) {
-      run_query(g, make_args(g, mode, m, sl.r.p, n_vars, i_vars, i_var, sl.i_a.p, sl.out_f64.p, sl.i_b.p), g->s_comp);
+      run_query(g, make_args(g, mode, m, sl.r.p, n_vars, i_vars, i_var, sl.i_a.p, sl.out_f64.p, sl.i_b.p, fused ? sl.r1.p : nullptr), g->s_comp);
     };
     auto d2h = [&](Slot& sl, int64_t off, int64_t m, bool merge) {
       if (mode != QM_NEAREST && mode != QM_INTERP_ICELL)
@@ -1384,15 +1395,21 @@ int query_host(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars
       const void* src = f64_out ? (const void*)sl.out_f64.p : (const void*)sl.i_b.p;
       if (!merge || mode == QM_NEAREST) {
         CU(cudaMemcpyAsync(dst, src, (size_t)m * row_bytes, cudaMemcpyDeviceToHost, g->s_out));
+        if (fused) CU(cudaMemcpyAsync(out2_f64 + off, sl.r1.p, (size_t)m * 8, cudaMemcpyDeviceToHost, g->s_out));
         return;
       }
       // some queries of this chunk were not found: their rows stay untouched (:447, :461, :492)
-      char* st = (char*)stage_buffer(g, (size_t)g->host_chunk * row_bytes);
+      char* st = (char*)stage_buffer(g, (size_t)g->host_chunk * (row_bytes + (fused ? 8 : 0)));
+      char* st2 = st + (size_t)g->host_chunk * row_bytes;
       CU(cudaMemcpyAsync(st, src, (size_t)m * row_bytes, cudaMemcpyDeviceToHost, g->s_out));
+      if (fused) CU(cudaMemcpyAsync(st2, sl.r1.p, (size_t)m * 8, cudaMemcpyDeviceToHost, g->s_out));
       CU(cudaStreamSynchronize(g->s_out));
       const int32_t* ic = i_cell + off;
       for (int64_t i = 0; i < m; ++i)
-        if (ic[i] >= 1) std::memcpy(dst + (size_t)i * row_bytes, st + (size_t)i * row_bytes, row_bytes);
+        if (ic[i] >= 1) {
+          std::memcpy(dst + (size_t)i * row_bytes, st + (size_t)i * row_bytes, row_bytes);
+          if (fused) std::memcpy(out2_f64 + off + i, st2 + (size_t)i * 8, 8);
+        }
     };
     return run_pipeline(g, n, CNT_NOT_FOUND, h2d, compute, d2h);
   });
@@ -1420,6 +1437,10 @@ int iu_b200_interpolate_scalar_at_batch(iu_b200_grid* g, int64_t n, const double
 int iu_b200_interpolate_at_icell_batch(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
                                        double* var_at_r, const int32_t* i_cell) {
   return query_host(g, QM_INTERP_ICELL, n, r, n_vars, i_vars, 0, const_cast<int32_t*>(i_cell), var_at_r, nullptr);
+}
+int iu_b200_interpolate_and_cell_scalar_at_batch(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
+                                                 int i_cell_var, double* var_at_r, double* cell_res, int32_t* i_cell) {
+  return query_host(g, QM_INTERP_CELL, n, r, n_vars, i_vars, i_cell_var, i_cell, var_at_r, nullptr, cell_res);
 }
 int iu_b200_get_cell_scalar_at_batch(iu_b200_grid* g, int64_t n, const double* r, int i_var, int32_t* i_guess, double* res) {
   return query_host(g, QM_CELL_F64, n, r, 0, nullptr, i_var, i_guess, res, nullptr);

@@ -30,7 +30,9 @@ enum QueryMode : int {
   QM_INTERP = 2,        // iu_interpolate_at                   -> i_cell, out_f64 (n_vars per query)
   QM_CELL_F64 = 3,      // iu_get_cell_scalar_at               -> i_cell, out_f64
   QM_CELL_I32 = 4,      // iu_get_icell_scalar_at              -> i_cell, out_i32
-  QM_INTERP_ICELL = 5   // iu_interpolate_at_icell (cells given, no search)
+  QM_INTERP_ICELL = 5,  // iu_interpolate_at_icell (cells given, no search)
+  QM_INTERP_CELL = 6    // iu_interpolate_at followed by iu_get_cell_scalar_at with the found cell as hint, in one pass
+                        //                                     -> i_cell, out_f64 (n_vars per query), out2_f64
 };
 
 // counters (device, unsigned long long each)
@@ -89,7 +91,9 @@ struct QueryArgs {
   const uint32_t* perm = nullptr;   // processing order (Morton-sorted), or null
   int32_t* i_cell = nullptr;        // inout (const for QM_INTERP_ICELL)
   double* out_f64 = nullptr;
+  double* out2_f64 = nullptr;       // QM_INTERP_CELL: cell-data scalar per query
   int32_t* out_i32 = nullptr;
+  int cell_var = 0;                 // QM_INTERP_CELL: 0-based cell_data column
   int n_vars = 0;
   int ivars[MAX_VARS] = {0};        // 0-based columns
   int max_steps = 1 << 20;

@@ -19,6 +19,8 @@
 //   k_pack_point_data, k_export_geometry, k_generate_queries: plumbing
 #include <cub/device/device_radix_sort.cuh>
 
+#include <cstdlib>
+
 #include "device.h"
 
 namespace iu {
@@ -935,9 +937,11 @@ struct QueryKernelParams {
   const uint32_t* perm;
   int32_t* i_cell;
   double* out_f64;
+  double* out2_f64;               // QM_INTERP_CELL: the cell-data scalar of each query
   int32_t* out_i32;
   int64_t n;
   int n_cells;
+  int cell_var;                   // QM_INTERP_CELL: 0-based cell_data column
   int pd_stride;
   int n_vars;
   int max_steps;
@@ -993,12 +997,12 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
     pid[0] = c.x; pid[1] = c.y; pid[2] = c.z; pid[3] = c.w;
     vol = __ldg(R + L::VOL);
   }
-  if (MODE != QM_INTERP_ICELL) ST_STREAM(P.i_cell + i, orig);
+  if (MODE != QM_INTERP_ICELL && MODE != QM_INTERP_CELL) ST_STREAM(P.i_cell + i, orig);
   if (MODE == QM_CELL_F64) {
     ST_STREAM(P.out_f64 + i, __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));          // :447
   } else if (MODE == QM_CELL_I32) {
     ST_STREAM(P.out_i32 + i, __ldg(P.icd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));         // :461
-  } else if (MODE == QM_INTERP || MODE == QM_INTERP_ICELL) {                           // :498-527
+  } else if (MODE == QM_INTERP || MODE == QM_INTERP_ICELL || MODE == QM_INTERP_CELL) {   // :498-527
     V3 p[PPC];
     if (PPC == 4) ld3x4(R + L::PTS, p); else ld3n<PPC>(R + L::PTS, p);
     Weights<CT> W;
@@ -1056,6 +1060,20 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
         for (int k = 0; k < PPC; ++k) d[k] = __ldg(P.pd + (size_t)pid[k] * P.pd_stride + P.ivars[v]);
         ST_STREAM(out + v, W.apply(d));
       }
+    }
+    if (MODE == QM_INTERP_CELL) {
+      // The second call of the composition, iu_get_cell_scalar_at with the cell just found as the hint (:437-448):
+      // iu_get_cell walks again, from that cell's centre (:424-432).  The record is still in L1 and the walk ends in
+      // its first step, except for a query within rounding of a face, which may end in the neighbour - exactly as the
+      // two-call sequence would.
+      const D4 c1 = ld256(P.cen32 + 4 * (size_t)(ic - 1));
+      V3 r_p; int ic2, n_steps = 0, status; bool early;
+      walk_ray<PPC>(P.rec, V3{c1.x, c1.y, c1.z}, V3{qx, qy, qz}, ic, P.max_steps, nullptr, ic2, r_p, n_steps, status, early);
+      if (!early && n_steps > P.max_steps) { ic2 = IU_WALK_LIMIT; atomicAdd(P.counters + CNT_WALK_LIMIT, 1ULL); }
+      if (ic2 < 1) { ST_STREAM(P.i_cell + i, ic2); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); return; }   // :446, res untouched
+      const int orig2 = ic2 == ic ? orig : __ldg(reinterpret_cast<const int32_t*>(P.rec + (size_t)(ic2 - 1) * L::STRIDE) + L::ORG_I);
+      ST_STREAM(P.i_cell + i, orig2);
+      ST_STREAM(P.out2_f64 + i, __ldg(P.cd + (size_t)P.cell_var * P.n_cells + (orig2 - 1)));              // :447
     }
   }
 }
@@ -1362,6 +1380,13 @@ void launch_query_ct(int mode, const QueryKernelParams& P, int depth, cudaStream
         default: launch_query_inst<CT, QM_INTERP, 0>(P, depth, s); break;
       }
       break;
+    case QM_INTERP_CELL:
+      switch (P.n_vars) {
+        case 4: launch_query_inst<CT, QM_INTERP_CELL, 4>(P, depth, s); break;
+        case 8: launch_query_inst<CT, QM_INTERP_CELL, 8>(P, depth, s); break;
+        default: launch_query_inst<CT, QM_INTERP_CELL, 0>(P, depth, s); break;
+      }
+      break;
     case QM_INTERP_ICELL:
       switch (P.n_vars) {
         case 1: launch_query_inst<CT, QM_INTERP_ICELL, 1>(P, depth, s); break;
@@ -1490,7 +1515,10 @@ int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t
   for (int k = 0; k < 3; ++k) { const double ext = g.rmax[k] - g.rmin[k]; sc[k] = ext > 0 ? nb / ext : 0.0; }
   k_morton_keys<<<(unsigned)std::min<int64_t>(blocks_for(n, 256), 148 * 32), 256, 0, s>>>(n, r, g.rmin[0], g.rmin[1], g.rmin[2], sc[0], sc[1], sc[2], bits, planar, keys, idx);
   const int end_bit = planar ? 2 * bits : 3 * bits;
-  cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const uint32_t*)keys, keys_alt, (const uint32_t*)idx, idx_alt, n, 0, end_bit, s);
+  // experiment knob: ignore the lowest key bits (queries of one coarse key cell keep their input order)
+  static const int drop_bits = [] { const char* e = std::getenv("IU_B200_SORT_DROP_BITS"); return e ? std::atoi(e) : 0; }();
+  const int begin_bit = drop_bits > 0 && drop_bits < end_bit ? drop_bits : 0;
+  cub::DeviceRadixSort::SortPairs(temp, temp_bytes, (const uint32_t*)keys, keys_alt, (const uint32_t*)idx, idx_alt, n, begin_bit, end_bit, s);
   if (end_bit_out) *end_bit_out = end_bit;
   // cub one-sweep: 1 histogram + 1 scan-ish + ceil(end_bit/8) passes; counted conservatively
   return 1 + 2 + (end_bit + 7) / 8;
@@ -1514,10 +1542,11 @@ int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   P.rec = g.rec; P.dev_of_orig = g.dev_of_orig; P.orig_of_dev = g.orig_of_dev;
   P.pd = g.pd; P.cd = g.cd; P.icd = g.icd; P.counters = g.counters;
   P.r = a.r; P.perm = a.perm; P.i_cell = a.i_cell; P.out_f64 = a.out_f64; P.out_i32 = a.out_i32;
+  P.out2_f64 = a.out2_f64; P.cell_var = a.cell_var;
   P.n = a.n; P.n_cells = g.n_cells; P.pd_stride = g.pd_stride; P.n_vars = a.n_vars; P.max_steps = a.max_steps;
   for (int v = 0; v < MAX_VARS; ++v) P.ivars[v] = a.ivars[v];
   P.pairs = 0;
-  if ((a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL) && a.n_vars % 2 == 0 && g.pd_stride % 2 == 0) {
+  if ((a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL || a.mode == QM_INTERP_CELL) && a.n_vars % 2 == 0 && g.pd_stride % 2 == 0) {
     P.pairs = 1;
     for (int v = 0; v < a.n_vars; v += 2)
       if (a.ivars[v] % 2 != 0 || a.ivars[v + 1] != a.ivars[v] + 1) P.pairs = 0;

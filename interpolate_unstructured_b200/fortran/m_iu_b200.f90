@@ -220,6 +220,21 @@ module m_iu_b200
        integer(c_int) :: rc
      end function c_interpolate_at_icell_batch
 
+     function c_interp_and_cell_scalar_batch(grid, n, r, n_vars, i_vars, i_cell_var, var_at_r, cell_res, i_cell) &
+          bind(C, name="iu_b200_interpolate_and_cell_scalar_at_batch") result(rc)
+       import
+       type(c_ptr), value :: grid
+       integer(c_int64_t), value :: n
+       real(c_double), intent(in) :: r(3, *)
+       integer(c_int), value :: n_vars
+       integer(c_int32_t), intent(in) :: i_vars(*)
+       integer(c_int), value :: i_cell_var
+       real(c_double), intent(inout) :: var_at_r(n_vars, *)
+       real(c_double), intent(inout) :: cell_res(*)
+       integer(c_int32_t), intent(inout) :: i_cell(*)
+       integer(c_int) :: rc
+     end function c_interp_and_cell_scalar_batch
+
      function c_get_cell_scalar_at_batch(grid, n, r, i_var, i_guess, res) &
           bind(C, name="iu_b200_get_cell_scalar_at_batch") result(rc)
        import
@@ -304,6 +319,7 @@ module m_iu_b200
   public :: iu_get_cell_batch
   public :: iu_get_cell_through_neighbors_batch
   public :: iu_get_cell_scalar_at_batch
+  public :: iu_interpolate_and_cell_scalar_at_batch
   public :: iu_get_icell_scalar_at_batch
   public :: iu_interpolate_at_batch
   public :: iu_interpolate_scalar_at_batch
@@ -559,6 +575,22 @@ contains
     call check(c_interpolate_at_icell_batch(ug%handle, n, r, n_vars, i_vars, var_at_r, i_cell), &
          "iu_interpolate_at_icell")
   end subroutine iu_interpolate_at_icell_batch
+
+  !> iu_interpolate_at (:480-495) followed by iu_get_cell_scalar_at (:437-448) with the cell just
+  !> found as i_guess, for n points in one pass over the queries
+  subroutine iu_interpolate_and_cell_scalar_at_batch(ug, n, r, n_vars, i_vars, i_cell_var, var_at_r, cell_res, i_cell)
+    type(iu_grid_t), intent(in) :: ug
+    integer(int64), intent(in)  :: n
+    real(dp), intent(in)        :: r(3, n)
+    integer, intent(in)         :: n_vars
+    integer, intent(in)         :: i_vars(n_vars)
+    integer, intent(in)         :: i_cell_var
+    real(dp), intent(inout)     :: var_at_r(n_vars, n)
+    real(dp), intent(inout)     :: cell_res(n)
+    integer, intent(inout)      :: i_cell(n)
+    call check(c_interp_and_cell_scalar_batch(ug%handle, n, r, n_vars, i_vars, i_cell_var, var_at_r, cell_res, i_cell), &
+         "iu_interpolate_and_cell_scalar_at")
+  end subroutine iu_interpolate_and_cell_scalar_at_batch
 
   !> iu_get_cell_scalar_at (:437-448) for n points
   subroutine iu_get_cell_scalar_at_batch(ug, n, r, i_var, i_guess, res)

@@ -855,6 +855,17 @@ void iu_oracle_get_cell_scalar_at(void* h, int64_t n, const double* r, int i_var
     if (i_guess[i] >= 1) res[i] = g.cell_data[(size_t)(i_var - 1) * g.n_cells + (i_guess[i] - 1)];
   }
 }
+// the same over OpenMP threads (bench.py's CPU leg of config C5)
+void iu_oracle_get_cell_scalar_at_mt(void* h, int64_t n, const double* r, int i_var, int* i_guess, double* res, int nn_mode,
+                                     int nthreads) {
+  const Grid& g = *(Grid*)h;
+  int nt = eff_threads(nthreads); (void)nt;
+#pragma omp parallel for num_threads(nt) schedule(static)
+  for (int64_t i = 0; i < n; ++i) {
+    get_cell(g, r + 3 * i, i_guess[i], nn_mode, nullptr, nullptr);
+    if (i_guess[i] >= 1) res[i] = g.cell_data[(size_t)(i_var - 1) * g.n_cells + (i_guess[i] - 1)];
+  }
+}
 void iu_oracle_get_icell_scalar_at(void* h, int64_t n, const double* r, int i_var, int* i_guess, int* res, int nn_mode) {
   const Grid& g = *(Grid*)h;
   for (int64_t i = 0; i < n; ++i) {
@@ -898,6 +909,59 @@ void iu_oracle_integrate_along_field(void* h, int64_t n, int ndim, int nvar, int
     integrate_along_field(g, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, rtol, atol, reverse != 0, y + ny * i,
                           y_field + nf * i, n_steps[i], axisymmetric != 0, i_icell_mask, mask_value,
                           boundary_material ? boundary_material + i : nullptr, nn_mode);
+}
+
+// get_cell_neighbors, convert_to_binary.py:118-162.  cells0 (n_cells, ppc) 0-based as on disk; neigh0 (n_cells, ppc)
+// receives the 0-based neighbour behind face i = vertices cell[(i + k) % ppc], k = 0..n_points_face-1, or -1.
+// Coincident points are merged first (np.unique(points, axis=0), :130: only the equivalence classes matter, so the
+// class id here is the lowest point index of the class, not numpy's rank).  The reference's dict of sorted face
+// tuples (:139-160) is restated as a sort of (face, cell) records: a face with exactly two cells links them, any
+// other count leaves -1, which is what `len(all_cells) == 2` does.
+int iu_oracle_cell_neighbors(int n_points, int n_cells, int ppc, int n_points_face, const double* points, const int* cells0,
+                             int* neigh0) {
+  if (ppc < 3 || ppc > 4 || n_points_face < 2 || n_points_face > 3) { g_err = "unsupported cell shape"; return -1; }
+  std::vector<int> order(n_points), cls(n_points);
+  for (int i = 0; i < n_points; ++i) order[i] = i;
+  auto key_less = [&](int a, int b) {
+    const double* pa = points + 3 * (size_t)a; const double* pb = points + 3 * (size_t)b;
+    for (int k = 0; k < 3; ++k) { if (pa[k] < pb[k]) return true; if (pa[k] > pb[k]) return false; }
+    return a < b;
+  };
+  std::sort(order.begin(), order.end(), key_less);
+  for (int j = 0; j < n_points; ++j) {
+    const int i = order[j];
+    bool same = false;
+    if (j > 0) {
+      const double* pa = points + 3 * (size_t)order[j - 1]; const double* pb = points + 3 * (size_t)i;
+      same = pa[0] == pb[0] && pa[1] == pb[1] && pa[2] == pb[2];
+    }
+    cls[i] = same ? cls[order[j - 1]] : i;
+  }
+  struct Face { uint32_t v[3]; uint32_t slot; };   // slot = cell * ppc + face index
+  const size_t nf = (size_t)n_cells * ppc;
+  std::vector<Face> faces(nf);
+  for (size_t c = 0; c < (size_t)n_cells; ++c)
+    for (int i = 0; i < ppc; ++i) {
+      Face f; f.v[2] = 0; f.slot = (uint32_t)(c * ppc + i);
+      for (int k = 0; k < n_points_face; ++k) f.v[k] = (uint32_t)cls[cells0[c * ppc + (i + k) % ppc]];
+      std::sort(f.v, f.v + n_points_face);
+      faces[c * ppc + i] = f;
+    }
+  std::sort(faces.begin(), faces.end(), [](const Face& a, const Face& b) {
+    for (int k = 0; k < 3; ++k) if (a.v[k] != b.v[k]) return a.v[k] < b.v[k];
+    return a.slot < b.slot;
+  });
+  for (size_t i = 0; i < nf; ++i) neigh0[i] = -1;
+  for (size_t i = 0; i < nf;) {
+    size_t j = i + 1;
+    while (j < nf && faces[j].v[0] == faces[i].v[0] && faces[j].v[1] == faces[i].v[1] && faces[j].v[2] == faces[i].v[2]) ++j;
+    if (j - i == 2) {
+      neigh0[faces[i].slot] = (int)(faces[i + 1].slot / ppc);
+      neigh0[faces[i + 1].slot] = (int)(faces[i].slot / ppc);
+    }
+    i = j;
+  }
+  return 0;
 }
 
 int iu_oracle_max_threads() {

@@ -49,12 +49,15 @@ def lib():
         L.iu_oracle_interpolate_at.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_dp, c_ip, C.c_int, C.c_int]
         L.iu_oracle_interpolate_at_icell.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_dp, c_ip]
         L.iu_oracle_get_cell_scalar_at.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_dp, C.c_int]
+        L.iu_oracle_get_cell_scalar_at_mt.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_dp, C.c_int, C.c_int]
         L.iu_oracle_get_icell_scalar_at.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_ip, C.c_int]
         L.iu_oracle_walk.argtypes = [C.c_void_p, C.c_int64, C.c_int, c_dp, c_dp, c_ip, c_ip, c_dp, c_ip, c_ip, C.c_int]
         L.iu_oracle_point_is_inside_cell.argtypes = [C.c_void_p, C.c_int64, c_dp, c_ip, c_ip]
         L.iu_oracle_integrate_along_field.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_int, c_ip, C.c_double, C.c_double,
                                                       C.c_int, C.c_double, C.c_double, C.c_int, c_dp, c_dp, c_ip, C.c_int, C.c_int,
                                                       C.c_int, c_ip, C.c_int, C.c_int]
+        L.iu_oracle_cell_neighbors.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_ip, c_ip]
+        L.iu_oracle_max_threads.restype = C.c_int
         L.iu_oracle_benchmark_pass.restype = C.c_double
         L.iu_oracle_benchmark_pass.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_dp, c_ip, C.c_int]
         _lib = L
@@ -75,6 +78,19 @@ def _f64(a):
 
 def _i32(a):
     return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def cell_neighbors(cells0, points, cell_type):
+    """get_cell_neighbors (convert_to_binary.py:118-162): 0-based (Nc, ppc) neighbour table, -1 = none."""
+    cells0 = _i32(cells0)
+    points = _f64(points)
+    nc, ppc = cells0.shape
+    npf = {"triangle": 2, "quad": 2, "tetra": 3}[cell_type]
+    out = np.empty((nc, ppc), dtype=np.int32)
+    rc = lib().iu_oracle_cell_neighbors(len(points), nc, ppc, npf, _d(points), _i(cells0), _i(out))
+    if rc != 0:
+        raise RuntimeError(lib().iu_oracle_last_error().decode())
+    return out
 
 
 class OracleGrid:
@@ -220,12 +236,12 @@ class OracleGrid:
         lib().iu_oracle_interpolate_at_icell(self.h, len(r), _d(r), len(iv), _i(iv), _d(out), _i(ic))
         return out
 
-    def get_cell_scalar_at(self, r, i_var, i_guess=None, res=None, nn="kdtree2"):
+    def get_cell_scalar_at(self, r, i_var, i_guess=None, res=None, nn="kdtree2", nthreads=1):
         r = _f64(r)
         n = len(r)
         ic = np.zeros(n, dtype=np.int32) if i_guess is None else _i32(i_guess).copy()
         out = np.zeros(n) if res is None else _f64(res).copy()
-        lib().iu_oracle_get_cell_scalar_at(self.h, n, _d(r), int(i_var), _i(ic), _d(out), 0 if nn == "kdtree2" else 1)
+        lib().iu_oracle_get_cell_scalar_at_mt(self.h, n, _d(r), int(i_var), _i(ic), _d(out), 0 if nn == "kdtree2" else 1, int(nthreads))
         return out, ic
 
     def get_icell_scalar_at(self, r, i_var, i_guess=None, res=None, nn="kdtree2"):

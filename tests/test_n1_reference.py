@@ -12,6 +12,7 @@ import numpy as np
 import pytest
 
 from interpolate_unstructured_b200 import api, binda, meshgen
+from oracle import oracle
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 GOLD = os.path.join(HERE, "golden")
@@ -45,6 +46,7 @@ def test_neighbour_builders_reproduce_reference_fixture_tables(name):
     pts, cells, ct = ents["points"].data.astype(np.float64), ents["cells"].data, ents["cells"].metadata
     assert (api.build_cell_neighbors(cells, pts, ct) == ents["cell_neighbors"].data).all()
     assert (meshgen.cell_neighbors(cells, pts, ct) == ents["cell_neighbors"].data).all()
+    assert (oracle.cell_neighbors(cells, pts, ct) == ents["cell_neighbors"].data).all()     # the oracle's restatement (bench.py's reference arm)
 
 
 def test_neighbour_builders_match_reference_on_118k_tets_with_duplicate_points():
@@ -56,6 +58,8 @@ def test_neighbour_builders_match_reference_on_118k_tets_with_duplicate_points()
     assert hashlib.sha256(np.ascontiguousarray(nb_cpp, dtype=np.int32).tobytes()).hexdigest() == gold["sha256_int32"]
     nb_np = meshgen.cell_neighbors(cells, pts, "tetra")
     assert hashlib.sha256(np.ascontiguousarray(nb_np, dtype=np.int32).tobytes()).hexdigest() == gold["sha256_int32"]
+    nb_or = oracle.cell_neighbors(cells, pts, "tetra")
+    assert hashlib.sha256(np.ascontiguousarray(nb_or, dtype=np.int32).tobytes()).hexdigest() == gold["sha256_int32"]
 
 
 @pytest.mark.skipif(not HAVE_REF, reason="reference tree not present (GPU box)")
@@ -84,3 +88,4 @@ def test_cpp_builder_equals_reference_function_live():
                 cells2[c, k] = len(pts) + j
         want = ref["get_cell_neighbors"](cells2, pts2, npf)
         assert (api.build_cell_neighbors(cells2, pts2, ct) == want).all()
+        assert (oracle.cell_neighbors(cells2, pts2, ct) == want).all()

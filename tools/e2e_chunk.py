@@ -2,7 +2,7 @@ import sys, time, numpy as np
 sys.path.insert(0, "/root/repo")
 import torch, bench
 from interpolate_unstructured_b200 import api
-pts, cells, nb, pd, qlo, qhi = bench.make_mesh(119)
+wl = bench.Workload("C3").mesh(); pts, cells, nb, pd, qlo, qhi = wl.pts, wl.cells, wl.nb, wl.pd, wl.qlo, wl.qhi
 g = api.Grid.from_arrays("tetra", pts, cells, nb, pd, device=0)
 ne = 100_000_000
 r = torch.empty((ne, 3), dtype=torch.float64, device="cuda")

@@ -27,7 +27,9 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
-    pts, cells, nb, pd, qlo, qhi = bench.make_mesh(a.mesh_n)
+    wl = bench.Workload("C3", a.mesh_n).mesh()
+    pts, cells, nb, pd, qlo, qhi = wl.pts, wl.cells, wl.nb, wl.pd, wl.qlo, wl.qhi
+    N_VARS, I_VARS = wl.n_vars, wl.i_vars
     g = api.Grid.from_arrays("tetra", pts, cells, nb, pd, device=0)
     g.set_option(api.OPT_TIME_KERNELS, 1)
     nq = int(a.queries)
@@ -35,7 +37,7 @@ def main():
     g.generate_queries_dev(r, first=0, seed=20261104, lo=qlo, hi=qhi)
     ic = torch.zeros(nq, dtype=torch.int32, device=dev)
     idx = torch.zeros(nq, dtype=torch.int32, device=dev)
-    out = torch.empty((nq, bench.N_VARS), dtype=torch.float64, device=dev)
+    out = torch.empty((nq, N_VARS), dtype=torch.float64, device=dev)
     hint = torch.zeros(nq, dtype=torch.int32, device=dev)
     g.iu_get_cell_dev(r, hint)
 
@@ -48,14 +50,14 @@ def main():
 
     def interp():
         ic.zero_()
-        g.iu_interpolate_at_dev(r, bench.I_VARS, out, ic)
+        g.iu_interpolate_at_dev(r, I_VARS, out, ic)
 
     def warm():
         ic.copy_(hint)
-        g.iu_interpolate_at_dev(r, bench.I_VARS, out, ic)
+        g.iu_interpolate_at_dev(r, I_VARS, out, ic)
 
     def icell():
-        g.iu_interpolate_at_icell_dev(r, bench.I_VARS, out, hint)
+        g.iu_interpolate_at_icell_dev(r, I_VARS, out, hint)
 
     # the same queries physically in Morton order (24-bit key like the library's), processed without a permutation
     def spread(v):
@@ -87,14 +89,14 @@ def main():
 
     def interp_ps():
         ic.zero_()
-        g.iu_interpolate_at_dev(rs, bench.I_VARS, out, ic)
+        g.iu_interpolate_at_dev(rs, I_VARS, out, ic)
 
     def warm_ps():
         ic.copy_(hs)
-        g.iu_interpolate_at_dev(rs, bench.I_VARS, out, ic)
+        g.iu_interpolate_at_dev(rs, I_VARS, out, ic)
 
     def icell_ps():
-        g.iu_interpolate_at_icell_dev(rs, bench.I_VARS, out, hs)
+        g.iu_interpolate_at_icell_dev(rs, I_VARS, out, hs)
 
     res = {}
     for name, fn in [("nearest_presorted", presorted(nearest_ps)), ("interp_presorted", presorted(interp_ps)),
