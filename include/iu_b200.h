@@ -84,7 +84,9 @@ extern "C" {
 #define IU_B200_STAT_NN_VOXEL_ENTRIES 12 /* sum of the candidate-list lengths */
 #define IU_B200_STAT_NN_TREE_QUERIES 13 /* cold queries that searched the kd-tree although a table exists */
 #define IU_B200_STAT_NN_VOXEL_BUILD_US 14 /* device time of the last table build */
-#define IU_B200_N_STATS 16
+#define IU_B200_STAT_DEVICES 15        /* GPUs holding a replica of the mesh (iu_b200_device_count) */
+#define IU_B200_STAT_REPLICATE_US 16   /* host time spent replicating the built mesh device to device */
+#define IU_B200_N_STATS 18
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */
 
@@ -116,6 +118,23 @@ int iu_b200_grid_create(const iu_b200_grid_desc* desc, iu_b200_grid** grid);
 /* iu_read_grid(filename, ug, coord_scale_factor) for *.binda files (:820-927, m_binda.f90):
  * reads the BINDA container, widens float32, applies the scale factor and the +1 index shift. */
 int iu_b200_grid_from_binda(const char* filename, double coord_scale_factor, int device, iu_b200_grid** grid);
+
+/* ---- one handle, several GPUs (the mesh is replicated, queries are split, no collective) ----
+ * iu_b200_grid_replicate copies the BUILT mesh (records, search structures, data tables) device to device
+ * (cudaMemcpyPeer) onto every listed GPU that does not hold it yet; n_devices <= 0 or devices == NULL means every
+ * visible GPU.  Afterwards every host-buffer *_batch call splits [0, n) into one contiguous slab per GPU and runs the
+ * slabs concurrently (one host thread per GPU, each with its own H2D | kernels | D2H pipeline); results are identical
+ * to the single-GPU handle's.  Column updates, added columns, names and options apply to every replica.  The *_dev
+ * entry points take pointers of ONE device: call them with the handle of that device's replica
+ * (iu_b200_grid_replica(grid, i), i = 0 .. iu_b200_device_count - 1; replica 0 is `grid` itself; info[7] of
+ * iu_b200_grid_info is its device).  Replicas are owned by `grid` and destroyed with it.
+ * iu_b200_grid_create_multi / _from_binda_multi = create on devices[0], then replicate. */
+int iu_b200_grid_replicate(iu_b200_grid* grid, int n_devices, const int* devices);
+int iu_b200_grid_create_multi(const iu_b200_grid_desc* desc, int n_devices, const int* devices, iu_b200_grid** grid);
+int iu_b200_grid_from_binda_multi(const char* filename, double coord_scale_factor, int n_devices, const int* devices,
+                                  iu_b200_grid** grid);
+int iu_b200_device_count(const iu_b200_grid* grid);
+iu_b200_grid* iu_b200_grid_replica(iu_b200_grid* grid, int i);
 
 int iu_b200_grid_destroy(iu_b200_grid* grid);
 

@@ -33,7 +33,7 @@ OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KE
 OPT_NN_VOXEL_DENSITY = 7
 STAT_NAMES = ["kernel_launches", "walk_limit_hits", "queries", "workspace_bytes", "mesh_bytes", "tree_depth",
               "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "nn_voxels", "nn_voxels_tree", "nn_voxel_entries",
-              "nn_tree_queries", "nn_voxel_build_us", "reserved15"]
+              "nn_tree_queries", "nn_voxel_build_us", "devices", "replicate_us", "reserved17"]
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)
@@ -63,6 +63,11 @@ _SIGNATURES = {
     "iu_b200_last_error": (C.c_char_p, []),
     "iu_b200_grid_create": (C.c_int, [C.POINTER(_Desc), C.POINTER(c_vp)]),
     "iu_b200_grid_from_binda": (C.c_int, [C.c_char_p, C.c_double, C.c_int, C.POINTER(c_vp)]),
+    "iu_b200_grid_replicate": (C.c_int, [c_vp, C.c_int, C.POINTER(C.c_int)]),
+    "iu_b200_grid_create_multi": (C.c_int, [C.POINTER(_Desc), C.c_int, C.POINTER(C.c_int), C.POINTER(c_vp)]),
+    "iu_b200_grid_from_binda_multi": (C.c_int, [C.c_char_p, C.c_double, C.c_int, C.POINTER(C.c_int), C.POINTER(c_vp)]),
+    "iu_b200_device_count": (C.c_int, [c_vp]),
+    "iu_b200_grid_replica": (c_vp, [c_vp, C.c_int]),
     "iu_b200_grid_destroy": (C.c_int, [c_vp]),
     "iu_b200_grid_info": (C.c_int, [c_vp, c_ip]),
     "iu_b200_grid_bounds": (C.c_int, [c_vp, c_dp, c_dp]),
@@ -265,17 +270,24 @@ class Grid:
 
     # ---- construction ------------------------------------------------------------------------
     @classmethod
-    def iu_read_grid(cls, filename, coord_scale_factor=1.0, device=-1):
-        """iu_read_grid(filename, ug, coord_scale_factor) for ``*.binda`` files (:820-927)."""
+    def iu_read_grid(cls, filename, coord_scale_factor=1.0, device=-1, devices=None):
+        """iu_read_grid(filename, ug, coord_scale_factor) for ``*.binda`` files (:820-927).  ``devices``: list of GPUs that
+        each get a replica of the mesh (the first one builds it)."""
         h = c_vp()
-        _check(lib().iu_b200_grid_from_binda(os.fsencode(str(filename)), float(coord_scale_factor), int(device), C.byref(h)))
+        if devices is not None:
+            arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+            _check(lib().iu_b200_grid_from_binda_multi(os.fsencode(str(filename)), float(coord_scale_factor), len(devices), arr, C.byref(h)))
+        else:
+            _check(lib().iu_b200_grid_from_binda(os.fsencode(str(filename)), float(coord_scale_factor), int(device), C.byref(h)))
         return cls(h.value)
 
     @classmethod
     def from_arrays(cls, cell_type, points, cells0, neighbors0, point_data=None, cell_data=None, icell_data=None,
-                    point_names=None, cell_names=None, icell_names=None, device=-1):
+                    point_names=None, cell_names=None, icell_names=None, device=-1, devices=None):
         """cells0 / neighbors0 are 0-based as on disk (+1 applied here like :871-872); data tables
-        are (n_rows, n_columns)."""
+        are (n_rows, n_columns).  ``devices``: GPUs that each get a replica (the first one builds the mesh)."""
+        if devices is not None:
+            device = devices[0]
         ct = CELL_TYPES.get(cell_type, cell_type)
         points = _f64(points, (3,))
         cells = np.ascontiguousarray(np.asarray(cells0, dtype=np.int64) + 1, dtype=np.int32)
@@ -308,9 +320,41 @@ class Grid:
                     raise ValueError("one name per data column expected")
                 for i, nm in enumerate(names):
                     _check(lib().iu_b200_set_data_name(g._h, kind, i + 1, str(nm).encode()))
+        if devices is not None and len(devices) > 1:
+            g.replicate(devices[1:])
+        return g
+
+    # ---- one handle, several GPUs ---------------------------------------------------------------
+    def replicate(self, devices=None):
+        """Copies the built mesh device to device onto ``devices`` (None = every visible GPU).  Afterwards the host-buffer
+        batch calls split their queries into one contiguous slab per GPU and run the slabs concurrently."""
+        if devices is None:
+            _check(lib().iu_b200_grid_replicate(self._h, 0, None))
+        else:
+            arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+            _check(lib().iu_b200_grid_replicate(self._h, len(devices), arr))
+        return self
+
+    @property
+    def device_count(self):
+        return int(lib().iu_b200_device_count(self._h))
+
+    def replica(self, i):
+        """Handle of the replica on the i-th GPU of this grid (0 = the grid itself), for the ``*_dev`` calls with tensors
+        of that GPU.  Owned by this grid: do not close it."""
+        h = lib().iu_b200_grid_replica(self._h, int(i))
+        if not h:
+            raise IndexError("replica index outside 0..device_count-1")
+        if i == 0:
+            return self
+        g = Grid(h)
+        g._borrowed = True
         return g
 
     def close(self):
+        if getattr(self, "_borrowed", False):
+            self._h = C.c_void_p(None)
+            return
         if getattr(self, "_h", None) is not None and self._h.value:
             lib().iu_b200_grid_destroy(self._h)
             self._h = C.c_void_p(None)

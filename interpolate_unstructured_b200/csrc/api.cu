@@ -6,12 +6,15 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <mutex>
 #include <new>
+#include <thread>
 
 #include "../../include/iu_b200.h"
 #include "device.h"
@@ -128,6 +131,10 @@ struct iu_b200_grid {
   cudaEvent_t ws_done = nullptr;
   cudaStream_t ws_stream = nullptr;
   bool ws_used = false;
+  // Further replicas of the mesh on other GPUs (iu_b200_grid_replicate): full single-device grids of their own.  The
+  // host-buffer batch calls split [0, n) into one contiguous slab per device and run them concurrently.
+  std::vector<iu_b200_grid*> replicas;
+  double replicate_ms = 0;
 };
 
 namespace {
@@ -226,6 +233,44 @@ int guarded(F&& f) {
   }
 }
 
+// applies a mutation to the further replicas of a multi-GPU handle once it succeeded on the primary
+template <class F>
+int on_replicas(iu_b200_grid* g, int rc, F&& f) {
+  if (rc != IU_B200_OK) return rc;
+  for (iu_b200_grid* r : g->replicas) {
+    const int rc2 = f(r);
+    if (rc2 != IU_B200_OK) return rc2;
+  }
+  return IU_B200_OK;
+}
+
+// Host-buffer batch calls of a multi-GPU handle: [0, n) is cut into one contiguous slab per device (multiples of 4
+// queries, so that every slab keeps the 32-byte alignment of the result rows) and f(grid of that device, offset, count)
+// runs on one host thread per device.  There is no exchange between the devices: every replica holds the whole mesh.
+constexpr int64_t MULTI_MIN_QUERIES = 1 << 16;
+template <class F>
+int run_slabs(iu_b200_grid* g, int64_t n, F&& f, int64_t min_n = MULTI_MIN_QUERIES) {
+  const int nd = g ? 1 + (int)g->replicas.size() : 1;
+  if (nd == 1 || n < min_n) return f(g, (int64_t)0, n);
+  const int64_t slab = ((n + nd - 1) / nd + 3) / 4 * 4;
+  std::vector<int> rcs(nd, IU_B200_OK);
+  std::vector<std::string> errs(nd);
+  std::vector<std::thread> threads;
+  for (int d = 0; d < nd; ++d) {
+    const int64_t off = (int64_t)d * slab, m = std::min(slab, n - off);
+    if (m <= 0) break;
+    iu_b200_grid* gd = d == 0 ? g : g->replicas[d - 1];
+    threads.emplace_back([&, d, gd, off, m]() {
+      rcs[d] = f(gd, off, m);
+      if (rcs[d] != IU_B200_OK) errs[d] = g_error;
+    });
+  }
+  for (std::thread& t : threads) t.join();
+  for (int d = 0; d < nd; ++d)
+    if (rcs[d] != IU_B200_OK) { set_error(errs[d]); return rcs[d]; }
+  return IU_B200_OK;
+}
+
 bool check_device_available() {
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);
@@ -313,6 +358,69 @@ void build_voxel_table(iu_b200_grid* g) {
   d.vox_lists = lists.take();
   v.lists = d.vox_lists;
   d.vox = v;
+}
+
+// streams, events and pinned counter snapshots of the host-buffer pipeline (current device = g->device)
+void init_pipeline(iu_b200_grid* g) {
+  CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&g->s_out, cudaStreamNonBlocking));
+  for (Slot& sl : g->slot) {
+    CU(cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&sl.comp_done, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&sl.out_done, cudaEventDisableTiming));
+  }
+  CU(cudaMallocHost((void**)&g->h_counters, N_SLOTS * CNT_N * sizeof(unsigned long long)));
+}
+
+// A replica of a built grid on another GPU: every device array is copied device to device (cudaMemcpyPeer: over
+// NVLink where the GPUs are peers), nothing is rebuilt.  The replica is a complete single-device grid.
+iu_b200_grid* clone_to_device(iu_b200_grid* src, int device) {
+  iu_b200_grid* g = new iu_b200_grid();
+  g->device = device;
+  try {
+    DeviceGuard guard(device);
+    const DeviceGrid& a = src->dg;
+    DeviceGrid& d = g->dg;
+    d = a;                                   // scalars; the pointers are replaced below
+    d.fat = d.centers4 = d.cen32 = d.rec = d.points = d.pd = d.cd = nullptr;
+    d.vox_lists = nullptr; d.vox.lists = nullptr; d.box = nullptr;
+    d.dev_of_orig = d.orig_of_dev = nullptr; d.icd = nullptr; d.counters = nullptr;
+    auto copy = [&](auto*& dst, const auto* from, size_t bytes) {
+      if (!from || bytes == 0) return;
+      CU(cudaMalloc((void**)&dst, bytes));
+      CU(cudaMemcpyPeerAsync(dst, device, from, src->device, bytes, nullptr));
+    };
+    const size_t n_slots = (size_t)a.n_leaves * LEAF;
+    copy(d.fat, a.fat, (size_t)a.n_internal * 32);
+    copy(d.centers4, a.centers4, n_slots * 24);
+    copy(d.cen32, a.cen32, n_slots * 32);
+    copy(d.box, a.box, std::max<size_t>(32, ((size_t)a.n_internal + a.n_leaves) * 8 * sizeof(float)));
+    copy(d.rec, a.rec, n_slots * rec_stride(a.ppc) * 8);
+    copy(d.points, a.points, (size_t)a.n_points * 24);
+    copy(d.dev_of_orig, a.dev_of_orig, ((size_t)a.n_cells + 1) * 4);
+    copy(d.orig_of_dev, a.orig_of_dev, n_slots * 4);
+    copy(d.vox_lists, a.vox_lists, (size_t)a.n_vox * VOX_K * 4);
+    d.vox.lists = d.vox_lists;
+    copy(d.pd, a.pd, (size_t)a.n_points * a.pd_stride * 8);
+    copy(d.cd, a.cd, (size_t)a.n_cells * a.cd_cap * 8);
+    copy(d.icd, a.icd, (size_t)a.n_cells * a.icd_cap * 4);
+    CU(cudaMalloc((void**)&d.counters, CNT_N * sizeof(unsigned long long)));
+    CU(cudaMemsetAsync(d.counters, 0, CNT_N * sizeof(unsigned long long), nullptr));
+    CU(cudaDeviceSynchronize());
+    g->point_names = src->point_names; g->cell_names = src->cell_names; g->icell_names = src->icell_names;
+    g->sort_mode = src->sort_mode; g->max_walk_steps = src->max_walk_steps; g->host_chunk = src->host_chunk;
+    g->dev_batch = src->dev_batch; g->dynamic_tiles = src->dynamic_tiles; g->voxel_density = src->voxel_density;
+    g->time_kernels = src->time_kernels;
+    for (int k = 0; k < 3; ++k) { g->cmin[k] = src->cmin[k]; g->cmax[k] = src->cmax[k]; }
+    g->vox_flagged = src->vox_flagged; g->vox_entries = src->vox_entries; g->vox_build_ms = 0;
+    g->mesh_bytes = src->mesh_bytes; g->tree_depth = src->tree_depth;
+    init_pipeline(g);
+  } catch (...) {
+    iu_b200_grid_destroy(g);
+    throw;
+  }
+  return g;
 }
 
 int create_from_arrays(int cell_type, int n_points, int n_cells, const double* points, const int32_t* cells,
@@ -408,6 +516,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     d.points = d_points.take();
     d_cells.release(); d_neigh.release(); d_centers.release();
     if (const char* env = std::getenv("IU_B200_NN_VOXEL_DENSITY")) g->voxel_density = std::max(0, std::atoi(env));
+    if (const char* env = std::getenv("IU_B200_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(env));   // experiment knob
     build_voxel_table(g);
     // data tables
     d.n_pd = n_pd;
@@ -433,15 +542,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     }
     g->mesh_bytes = (size_t)n_points * 24 + n_slots * (rec_stride(ppc) * 8 + 24 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + tree.box.size() * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
-    CU(cudaStreamCreateWithFlags(&g->s_in, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&g->s_comp, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&g->s_out, cudaStreamNonBlocking));
-    for (Slot& sl : g->slot) {
-      CU(cudaEventCreateWithFlags(&sl.in_done, cudaEventDisableTiming));
-      CU(cudaEventCreateWithFlags(&sl.comp_done, cudaEventDisableTiming));
-      CU(cudaEventCreateWithFlags(&sl.out_done, cudaEventDisableTiming));
-    }
-    CU(cudaMallocHost((void**)&g->h_counters, N_SLOTS * CNT_N * sizeof(unsigned long long)));
+    init_pipeline(g);
     return IU_B200_OK;
   });
   if (rc != IU_B200_OK) {
@@ -489,8 +590,63 @@ int iu_b200_grid_from_binda(const char* filename, double coord_scale_factor, int
   return IU_B200_OK;
 }
 
+int iu_b200_grid_replicate(iu_b200_grid* g, int n_devices, const int* devices) {
+  if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  if (!check_device_available()) return IU_B200_ECUDA;
+  int visible = 0;
+  cudaGetDeviceCount(&visible);
+  std::vector<int> want;
+  if (n_devices <= 0 || !devices) { for (int d = 0; d < visible; ++d) want.push_back(d); }   // every visible GPU
+  else want.assign(devices, devices + n_devices);
+  std::lock_guard<std::mutex> lock(g->mu);
+  return guarded([&]() {
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int dev : want) {
+      if (dev < 0 || dev >= visible) { set_error("device index outside 0..device count - 1"); return (int)IU_B200_EINVAL; }
+      bool have = dev == g->device;
+      for (iu_b200_grid* r : g->replicas) have = have || r->device == dev;
+      // test hook: a second replica on a GPU that already has one exercises the clone and the slab threads on a one-GPU box
+      const bool allow_same = std::getenv("IU_B200_ALLOW_SAME_DEVICE_REPLICAS") != nullptr;
+      if (have && !(allow_same && n_devices > 0 && devices)) continue;
+      { DeviceGuard guard(g->device); CU(cudaDeviceSynchronize()); }
+      g->replicas.push_back(clone_to_device(g, dev));
+    }
+    g->replicate_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return (int)IU_B200_OK;
+  });
+}
+
+int iu_b200_grid_create_multi(const iu_b200_grid_desc* desc, int n_devices, const int* devices, iu_b200_grid** grid) {
+  if (!desc || !grid) { set_error("null argument"); return IU_B200_EINVAL; }
+  iu_b200_grid_desc d0 = *desc;
+  if (n_devices > 0 && devices) d0.device = devices[0];
+  int rc = iu_b200_grid_create(&d0, grid);
+  if (rc != IU_B200_OK) return rc;
+  rc = iu_b200_grid_replicate(*grid, n_devices, devices);
+  if (rc != IU_B200_OK) { iu_b200_grid_destroy(*grid); *grid = nullptr; }
+  return rc;
+}
+
+int iu_b200_grid_from_binda_multi(const char* filename, double coord_scale_factor, int n_devices, const int* devices,
+                                  iu_b200_grid** grid) {
+  int rc = iu_b200_grid_from_binda(filename, coord_scale_factor, n_devices > 0 && devices ? devices[0] : 0, grid);
+  if (rc != IU_B200_OK) return rc;
+  rc = iu_b200_grid_replicate(*grid, n_devices, devices);
+  if (rc != IU_B200_OK) { iu_b200_grid_destroy(*grid); *grid = nullptr; }
+  return rc;
+}
+
+int iu_b200_device_count(const iu_b200_grid* g) { return g ? 1 + (int)g->replicas.size() : 0; }
+
+iu_b200_grid* iu_b200_grid_replica(iu_b200_grid* g, int i) {
+  if (!g || i < 0 || i > (int)g->replicas.size()) return nullptr;
+  return i == 0 ? g : g->replicas[i - 1];
+}
+
 int iu_b200_grid_destroy(iu_b200_grid* g) {
   if (!g) return IU_B200_OK;
+  for (iu_b200_grid* r : g->replicas) iu_b200_grid_destroy(r);
+  g->replicas.clear();
   {
     DeviceGuard guard(g->device);
     cudaDeviceSynchronize();
@@ -547,7 +703,7 @@ int iu_b200_set_data_name(iu_b200_grid* g, int kind, int i_var, const char* name
   std::vector<std::string>& names = kind == 0 ? g->point_names : kind == 1 ? g->cell_names : g->icell_names;
   if (i_var < 1 || i_var > (int)names.size()) { set_error("column outside 1..n"); return IU_B200_EINVAL; }
   names[i_var - 1] = name;
-  return IU_B200_OK;
+  return on_replicas(g, IU_B200_OK, [&](iu_b200_grid* r) { return iu_b200_set_data_name(r, kind, i_var, name); });
 }
 const char* iu_b200_point_data_name(const iu_b200_grid* g, int i_var) {
   if (!g || i_var < 1 || i_var > (int)g->point_names.size()) return nullptr;
@@ -592,7 +748,7 @@ extern "C" {
 int iu_b200_add_point_data(iu_b200_grid* g, const char* name, int* i_var) {
   if (!g || !name) { set_error("null argument"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);
-  return guarded([&]() {
+  int rc = guarded([&]() {
     DeviceGuard guard(g->device);
     DeviceGrid& d = g->dg;
     CU(cudaDeviceSynchronize());
@@ -620,12 +776,13 @@ int iu_b200_add_point_data(iu_b200_grid* g, const char* name, int* i_var) {
     if (i_var) *i_var = d.n_pd;
     return IU_B200_OK;
   });
+  return on_replicas(g, rc, [&](iu_b200_grid* r) { return iu_b200_add_point_data(r, name, nullptr); });
 }
 
 int iu_b200_add_cell_data(iu_b200_grid* g, const char* name, int* i_var) {
   if (!g || !name) { set_error("null argument"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);
-  return guarded([&]() {
+  int rc = guarded([&]() {
     DeviceGuard guard(g->device);
     CU(cudaDeviceSynchronize());
     append_zero_column(g->dg.cd, g->dg.n_cd, g->dg.cd_cap, (size_t)g->dg.n_cells);
@@ -633,12 +790,13 @@ int iu_b200_add_cell_data(iu_b200_grid* g, const char* name, int* i_var) {
     if (i_var) *i_var = g->dg.n_cd;
     return IU_B200_OK;
   });
+  return on_replicas(g, rc, [&](iu_b200_grid* r) { return iu_b200_add_cell_data(r, name, nullptr); });
 }
 
 int iu_b200_add_icell_data(iu_b200_grid* g, const char* name, int* i_var) {
   if (!g || !name) { set_error("null argument"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);
-  return guarded([&]() {
+  int rc = guarded([&]() {
     DeviceGuard guard(g->device);
     CU(cudaDeviceSynchronize());
     append_zero_column(g->dg.icd, g->dg.n_icd, g->dg.icd_cap, (size_t)g->dg.n_cells);
@@ -646,13 +804,14 @@ int iu_b200_add_icell_data(iu_b200_grid* g, const char* name, int* i_var) {
     if (i_var) *i_var = g->dg.n_icd;
     return IU_B200_OK;
   });
+  return on_replicas(g, rc, [&](iu_b200_grid* r) { return iu_b200_add_icell_data(r, name, nullptr); });
 }
 
 int iu_b200_update_point_data(iu_b200_grid* g, int col0, int n_cols, const double* data) {
   if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
   if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_pd) { set_error("point_data column range outside 1..n_point_data"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);
-  return guarded([&]() {
+  int rc = guarded([&]() {
     DeviceGuard guard(g->device);
     DevBuf<double> cols;
     cols.alloc((size_t)g->dg.n_points * n_cols);
@@ -661,30 +820,33 @@ int iu_b200_update_point_data(iu_b200_grid* g, int col0, int n_cols, const doubl
     CU(cudaDeviceSynchronize());
     return IU_B200_OK;
   });
+  return on_replicas(g, rc, [&](iu_b200_grid* r) { return iu_b200_update_point_data(r, col0, n_cols, data); });
 }
 
 int iu_b200_update_cell_data(iu_b200_grid* g, int col0, int n_cols, const double* data) {
   if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
   if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_cd) { set_error("cell_data column range outside 1..n_cell_data"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);
-  return guarded([&]() {
+  int rc = guarded([&]() {
     DeviceGuard guard(g->device);
     const size_t nc = (size_t)g->dg.n_cells;
     CU(cudaMemcpy(g->dg.cd + nc * (col0 - 1), data, nc * n_cols * 8, cudaMemcpyHostToDevice));
     return IU_B200_OK;
   });
+  return on_replicas(g, rc, [&](iu_b200_grid* r) { return iu_b200_update_cell_data(r, col0, n_cols, data); });
 }
 
 int iu_b200_update_icell_data(iu_b200_grid* g, int col0, int n_cols, const int32_t* data) {
   if (!g || !data) { set_error("null argument"); return IU_B200_EINVAL; }
   if (col0 < 1 || n_cols < 1 || col0 + n_cols - 1 > g->dg.n_icd) { set_error("icell_data column range outside 1..n_icell_data"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);
-  return guarded([&]() {
+  int rc = guarded([&]() {
     DeviceGuard guard(g->device);
     const size_t nc = (size_t)g->dg.n_cells;
     CU(cudaMemcpy(g->dg.icd + nc * (col0 - 1), data, nc * n_cols * 4, cudaMemcpyHostToDevice));
     return IU_B200_OK;
   });
+  return on_replicas(g, rc, [&](iu_b200_grid* r) { return iu_b200_update_icell_data(r, col0, n_cols, data); });
 }
 
 int iu_b200_download_point_data(iu_b200_grid* g, int col0, int n_cols, double* data) {
@@ -728,8 +890,12 @@ int iu_b200_download_icell_data(iu_b200_grid* g, int col0, int n_cols, int32_t* 
   });
 }
 
+static int set_option_one(iu_b200_grid* g, int option, int64_t value);
 int iu_b200_set_option(iu_b200_grid* g, int option, int64_t value) {
   if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
+  return on_replicas(g, set_option_one(g, option, value), [&](iu_b200_grid* r) { return set_option_one(r, option, value); });
+}
+static int set_option_one(iu_b200_grid* g, int option, int64_t value) {
   switch (option) {
     case IU_B200_OPT_SORT_QUERIES:
       if (value < 0 || value > 3) break;
@@ -797,14 +963,26 @@ int iu_b200_get_stats(iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
     stats[IU_B200_STAT_QUERY_KERNEL_NS] = (int64_t)g->timed_ns[0];
     stats[IU_B200_STAT_QUERY_KERNEL_LAUNCHES] = g->timed_launches[0];
     stats[IU_B200_STAT_SORT_NS] = (int64_t)g->timed_ns[1];
-    return IU_B200_OK;
+    stats[IU_B200_STAT_DEVICES] = 1 + (int64_t)g->replicas.size();
+    stats[IU_B200_STAT_REPLICATE_US] = (int64_t)(g->replicate_ms * 1e3);
+    // a multi-GPU handle reports the sums over its devices for the counters that add up
+    for (iu_b200_grid* r : g->replicas) {
+      int64_t rs[IU_B200_N_STATS];
+      const int rc = iu_b200_get_stats(r, rs);
+      if (rc != IU_B200_OK) return rc;
+      for (int k : {IU_B200_STAT_KERNEL_LAUNCHES, IU_B200_STAT_WALK_LIMIT_HITS, IU_B200_STAT_QUERIES, IU_B200_STAT_WORKSPACE_BYTES,
+                    IU_B200_STAT_MESH_BYTES, IU_B200_STAT_NN_TREE_QUERIES, IU_B200_STAT_NOT_FOUND, IU_B200_STAT_QUERY_KERNEL_NS,
+                    IU_B200_STAT_QUERY_KERNEL_LAUNCHES, IU_B200_STAT_SORT_NS})
+        stats[k] += rs[k];
+    }
+    return (int)IU_B200_OK;
   });
 }
 
 int iu_b200_reset_stats(iu_b200_grid* g) {
   if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);
-  return guarded([&]() {
+  int rc = guarded([&]() {
     DeviceGuard guard(g->device);
     CU(cudaDeviceSynchronize());
     unsigned long long c[CNT_N];
@@ -822,6 +1000,7 @@ int iu_b200_reset_stats(iu_b200_grid* g) {
     g->timed_launches[0] = g->timed_launches[1] = 0;
     return IU_B200_OK;
   });
+  return on_replicas(g, rc, [&](iu_b200_grid* r) { return iu_b200_reset_stats(r); });
 }
 
 }  // extern "C"
@@ -862,8 +1041,8 @@ void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
       g->keys.ensure(m); g->keys_alt.ensure(m); g->idx.ensure(m); g->idx_alt.ensure(m);
       g->sort_temp.ensure(sort_temp_bytes(m, end_bit));
       TimedScope ts(g, s, 1);
-      g->n_launches += launch_morton_sort(g->dg, m, b.r, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
-                                          g->sort_temp.p, g->sort_temp.n, nullptr, s);
+      g->n_launches += launch_morton_sort(g->dg, m, b.r, a.mode == QM_NEAREST ? nullptr : b.i_cell, g->keys.p, g->keys_alt.p,
+                                          g->idx.p, g->idx_alt.p, g->sort_temp.p, g->sort_temp.n, nullptr, s);
       ts.stop();
       b.perm = g->idx_alt.p;
       b.dynamic = g->dynamic_tiles;
@@ -936,7 +1115,7 @@ void run_walk(iu_b200_grid* g, WalkArgs a, cudaStream_t s) {
       g->keys.ensure(m); g->keys_alt.ensure(m); g->idx.ensure(m); g->idx_alt.ensure(m);
       g->sort_temp.ensure(sort_temp_bytes(m, end_bit));
       TimedScope ts(g, s, 1);
-      g->n_launches += launch_morton_sort(g->dg, m, b.r0, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
+      g->n_launches += launch_morton_sort(g->dg, m, b.r0, nullptr, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
                                           g->sort_temp.p, g->sort_temp.n, nullptr, s);
       ts.stop();
       b.perm = g->idx_alt.p;
@@ -1229,7 +1408,7 @@ void run_trace(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, co
     const int end_bit = morton_end_bit(g->dg);
     g->keys.ensure(n); g->keys_alt.ensure(n); g->idx.ensure(n); g->idx_alt.ensure(n);
     g->sort_temp.ensure(sort_temp_bytes(n, end_bit));
-    g->n_launches += launch_morton_sort(g->dg, n, g->tr_seed.p, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
+    g->n_launches += launch_morton_sort(g->dg, n, g->tr_seed.p, nullptr, g->keys.p, g->keys_alt.p, g->idx.p, g->idx_alt.p,
                                         g->sort_temp.p, g->sort_temp.n, nullptr, s);
     a.perm = g->idx_alt.p;
   }
@@ -1258,10 +1437,27 @@ int iu_b200_integrate_along_field_batch_dev(iu_b200_grid* g, int64_t n, int ndim
 
 // Host buffers: field lines are processed in chunks whose curves fit a bounded device buffer;
 // y / y_field go up first because columns beyond n_steps must come back untouched.
+static int trace_host_one(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field,
+                          double min_dx, double max_dx, int max_steps, double rtol, double atol, int reverse,
+                          double* y, double* y_field, int32_t* n_steps, int axisymmetric, int i_icell_mask,
+                          int mask_value, int32_t* boundary_material);
 int iu_b200_integrate_along_field_batch(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field,
                                         double min_dx, double max_dx, int max_steps, double rtol, double atol, int reverse,
                                         double* y, double* y_field, int32_t* n_steps, int axisymmetric, int i_icell_mask,
                                         int mask_value, int32_t* boundary_material) {
+  int rc = trace_args_ok(g, n, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, y, n_steps, i_icell_mask);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  const size_t ny = (size_t)(ndim + nvar) * max_steps, nf = (size_t)ndim * max_steps;
+  return run_slabs(g, n, [&](iu_b200_grid* gd, int64_t off, int64_t m) {
+    return trace_host_one(gd, m, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, rtol, atol, reverse, y + ny * off,
+                          y_field ? y_field + nf * off : nullptr, n_steps + off, axisymmetric, i_icell_mask, mask_value,
+                          boundary_material ? boundary_material + off : nullptr);
+  }, 4096);
+}
+static int trace_host_one(iu_b200_grid* g, int64_t n, int ndim, int nvar, int integrand, const int32_t* i_field,
+                          double min_dx, double max_dx, int max_steps, double rtol, double atol, int reverse,
+                          double* y, double* y_field, int32_t* n_steps, int axisymmetric, int i_icell_mask,
+                          int mask_value, int32_t* boundary_material) {
   int rc = trace_args_ok(g, n, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, y, n_steps, i_icell_mask);
   if (rc != IU_B200_OK || n == 0) return rc;
   std::lock_guard<std::mutex> lock(g->mu);
@@ -1358,8 +1554,8 @@ int run_pipeline(iu_b200_grid* g, int64_t n, int trigger, H2D&& h2d, COMPUTE&& c
   return IU_B200_OK;
 }
 
-int query_host(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
-               int32_t* i_cell, double* out_f64, int32_t* out_i32, double* out2_f64 = nullptr) {
+int query_host_one(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
+                   int32_t* i_cell, double* out_f64, int32_t* out_i32, double* out2_f64) {
   int rc = check_query_args(g, n, r, mode, n_vars, i_vars, i_var);
   if (rc != IU_B200_OK || n == 0) return rc;
   if (mode != QM_NEAREST && !i_cell) { set_error("null i_cell array"); return IU_B200_EINVAL; }
@@ -1415,6 +1611,16 @@ int query_host(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars
   });
 }
 
+int query_host(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_vars, const int32_t* i_vars, int i_var,
+               int32_t* i_cell, double* out_f64, int32_t* out_i32, double* out2_f64 = nullptr) {
+  const size_t row = mode == QM_INTERP || mode == QM_INTERP_ICELL || mode == QM_INTERP_CELL ? (size_t)std::max(n_vars, 0) : 1;
+  return run_slabs(g, n, [&](iu_b200_grid* gd, int64_t off, int64_t m) {
+    return query_host_one(gd, mode, m, r ? r + 3 * off : nullptr, n_vars, i_vars, i_var, i_cell ? i_cell + off : nullptr,
+                          out_f64 ? out_f64 + row * off : nullptr, out_i32 ? out_i32 + off : nullptr,
+                          out2_f64 ? out2_f64 + off : nullptr);
+  });
+}
+
 }  // namespace
 
 extern "C" {
@@ -1449,9 +1655,20 @@ int iu_b200_get_icell_scalar_at_batch(iu_b200_grid* g, int64_t n, const double* 
   return query_host(g, QM_CELL_I32, n, r, 0, nullptr, i_var, i_guess, nullptr, res);
 }
 
+static int walk_host_one(iu_b200_grid* g, int64_t n, int max_steps, const double* r0, const double* r1, const int32_t* ic0,
+                         int32_t* ic1, double* r_p, int32_t* n_steps, int32_t* status, int i_icell_mask);
 int iu_b200_get_cell_through_neighbors_batch(iu_b200_grid* g, int64_t n, int max_steps, const double* r0, const double* r1,
                                              const int32_t* ic0, int32_t* ic1, double* r_p, int32_t* n_steps,
                                              int32_t* status, int i_icell_mask) {
+  int rc = walk_args_ok(g, n, max_steps, r0, r1, ic0, ic1, r_p, n_steps, status, i_icell_mask);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  return run_slabs(g, n, [&](iu_b200_grid* gd, int64_t off, int64_t m) {
+    return walk_host_one(gd, m, max_steps, r0 + 3 * off, r1 + 3 * off, ic0 + off, ic1 + off, r_p + 3 * off, n_steps + off,
+                         status + off, i_icell_mask);
+  });
+}
+static int walk_host_one(iu_b200_grid* g, int64_t n, int max_steps, const double* r0, const double* r1, const int32_t* ic0,
+                         int32_t* ic1, double* r_p, int32_t* n_steps, int32_t* status, int i_icell_mask) {
   int rc = walk_args_ok(g, n, max_steps, r0, r1, ic0, ic1, r_p, n_steps, status, i_icell_mask);
   if (rc != IU_B200_OK || n == 0) return rc;
   std::lock_guard<std::mutex> lock(g->mu);

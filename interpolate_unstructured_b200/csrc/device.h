@@ -148,7 +148,8 @@ int launch_unpack_point_data(const DeviceGrid& g, double* cols, int col0, int n_
 int launch_repack_point_data(const double* old_pd, int old_stride, double* new_pd, int new_stride, int n_cols,
                              int n_points, cudaStream_t s);
 size_t sort_temp_bytes(int64_t n, int end_bit);
-int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t* keys, uint32_t* keys_alt,
+// hint: the batch's i_cell array or null; entries >= 1 set bit 31 of the query's permutation entry (kernels.cu: PERM_HINT_BIT)
+int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, const int32_t* hint, uint32_t* keys, uint32_t* keys_alt,
                        uint32_t* idx, uint32_t* idx_alt, void* temp, size_t temp_bytes, int* end_bit_out,
                        cudaStream_t s);
 int morton_end_bit(const DeviceGrid& g);

@@ -369,8 +369,13 @@ __device__ __forceinline__ uint32_t hilbert_table_entry(int state, int octant) {
 
 // bits = bits per dimension; planar meshes (z extent 0) use a 2-D Morton key, the others a Hilbert key
 // (IU_HILBERT = 0: Morton)
-__global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lox, double loy, double loz, double sx,
-                              double sy, double sz, int bits, int planar, uint32_t* __restrict__ keys,
+// idx = position of the query in the batch; bit 31 (PERM_HINT_BIT) is set when the query comes with a hint
+// (i_cell >= 1), so that k_query reads the scattered 4-byte hint only for those: a scattered read costs a whole
+// 128-byte DRAM line, which for an all-cold batch was a third of the kernel's DRAM reads (profiles/experiments/
+// r02d_dram_by_kernel_form.txt).  hint == nullptr: no flag (nearest-centre calls, ray batches, tracer seeds).
+constexpr uint32_t PERM_HINT_BIT = 0x80000000u;
+__global__ void k_morton_keys(int64_t n, const double* __restrict__ r, const int32_t* __restrict__ hint, double lox, double loy,
+                              double loz, double sx, double sy, double sz, int bits, int planar, uint32_t* __restrict__ keys,
                               uint32_t* __restrict__ idx) {
 #if IU_HILBERT
   __shared__ uint8_t s_tab[192];
@@ -399,7 +404,7 @@ __global__ void k_morton_keys(int64_t n, const double* __restrict__ r, double lo
 #endif
     }
     keys[i] = key;
-    idx[i] = (uint32_t)i;
+    idx[i] = (uint32_t)i | (hint && LD_STREAM(hint + i) >= 1 ? PERM_HINT_BIT : 0u);
   }
 }
 
@@ -1116,7 +1121,8 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       ++sub;
       if (t >= P.n) continue;
     } else if (t >= P.n) break;
-    const int64_t i = P.perm ? (int64_t)LD_STREAM(P.perm + t) : t;
+    const uint32_t pe = P.perm ? LD_STREAM(P.perm + t) : 0u;
+    const int64_t i = P.perm ? (int64_t)(pe & ~PERM_HINT_BIT) : t;
     // a query's 24 bytes as two scattered loads instead of three: 16 + 8 or 8 + 16 bytes, whichever is aligned
     double qx, qy, qz;
     {
@@ -1135,7 +1141,8 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       ST_STREAM(P.out_i32 + i, slot >= 0 ? __ldg(P.orig_of_dev + slot) : 0);
       continue;
     }
-    const int h = LD_STREAM(P.i_cell + i);
+    // through a permutation the scattered hint is read only where the key kernel saw one (PERM_HINT_BIT)
+    const int h = !P.perm || (pe & PERM_HINT_BIT) ? LD_STREAM(P.i_cell + i) : 0;
     if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); continue; }     // error stop, :490
     int start;
     if (MODE == QM_INTERP_ICELL) {
@@ -1506,14 +1513,14 @@ size_t sort_temp_bytes(int64_t n, int end_bit) {
   return bytes;
 }
 
-int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, uint32_t* keys, uint32_t* keys_alt, uint32_t* idx,
-                       uint32_t* idx_alt, void* temp, size_t temp_bytes, int* end_bit_out, cudaStream_t s) {
+int launch_morton_sort(const DeviceGrid& g, int64_t n, const double* r, const int32_t* hint, uint32_t* keys, uint32_t* keys_alt,
+                       uint32_t* idx, uint32_t* idx_alt, void* temp, size_t temp_bytes, int* end_bit_out, cudaStream_t s) {
   int bits, planar;
   morton_bits(g, bits, planar);
   const double nb = (double)(1u << bits);
   double sc[3];
   for (int k = 0; k < 3; ++k) { const double ext = g.rmax[k] - g.rmin[k]; sc[k] = ext > 0 ? nb / ext : 0.0; }
-  k_morton_keys<<<(unsigned)std::min<int64_t>(blocks_for(n, 256), 148 * 32), 256, 0, s>>>(n, r, g.rmin[0], g.rmin[1], g.rmin[2], sc[0], sc[1], sc[2], bits, planar, keys, idx);
+  k_morton_keys<<<(unsigned)std::min<int64_t>(blocks_for(n, 256), 148 * 32), 256, 0, s>>>(n, r, hint, g.rmin[0], g.rmin[1], g.rmin[2], sc[0], sc[1], sc[2], bits, planar, keys, idx);
   const int end_bit = planar ? 2 * bits : 3 * bits;
   // experiment knob: ignore the lowest key bits (queries of one coarse key cell keep their input order)
   static const int drop_bits = [] { const char* e = std::getenv("IU_B200_SORT_DROP_BITS"); return e ? std::atoi(e) : 0; }();

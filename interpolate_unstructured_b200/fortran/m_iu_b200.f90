@@ -65,6 +65,29 @@ module m_iu_b200
        integer(c_int) :: rc
      end function c_grid_from_binda
 
+     function c_grid_replicate(grid, n_devices, devices) bind(C, name="iu_b200_grid_replicate") result(rc)
+       import
+       type(c_ptr), value :: grid
+       integer(c_int), value :: n_devices
+       integer(c_int), intent(in) :: devices(*)
+       integer(c_int) :: rc
+     end function c_grid_replicate
+
+     function c_device_count(grid) bind(C, name="iu_b200_device_count") result(n)
+       import
+       type(c_ptr), value :: grid
+       integer(c_int) :: n
+     end function c_device_count
+
+     function c_export_geometry(grid, cell_points, normals, volume, centers) &
+          bind(C, name="iu_b200_export_geometry") result(rc)
+       import
+       type(c_ptr), value :: grid
+       type(c_ptr), value :: cell_points, normals, volume
+       real(c_double), intent(out) :: centers(3, *)
+       integer(c_int) :: rc
+     end function c_export_geometry
+
      function c_grid_destroy(grid) bind(C, name="iu_b200_grid_destroy") result(rc)
        import
        type(c_ptr), value :: grid
@@ -329,6 +352,8 @@ module m_iu_b200
   public :: iu_sync_cell_data
   public :: iu_sync_icell_data
   public :: iu_destroy_grid
+  public :: iu_device_count
+  public :: iu_get_cell_centers
   public :: iu_write_vtk
 
 contains
@@ -367,19 +392,28 @@ contains
 
   !> iu_read_grid, m_interp_unstructured.f90:820-927 (*.binda files only: the vtu -> binda
   !> conversion of :788-818 is a separate tool)
-  subroutine iu_read_grid(filename, ug, coord_scale_factor, device)
+  subroutine iu_read_grid(filename, ug, coord_scale_factor, device, devices)
     character(len=*), intent(in)   :: filename
     type(iu_grid_t), intent(inout) :: ug
     real(dp), intent(in), optional :: coord_scale_factor
     integer, intent(in), optional  :: device !< CUDA device ordinal (default: current)
+    !> several GPUs: devices(1) builds the mesh, the others receive a device-to-device replica;
+    !> the *_batch calls then split their queries into one slab per GPU
+    integer, intent(in), optional  :: devices(:)
     real(c_double) :: scale
     integer(c_int) :: dev
     integer(c_int32_t) :: info(8)
 
     scale = 1.0_dp; if (present(coord_scale_factor)) scale = coord_scale_factor
     dev = -1; if (present(device)) dev = device
+    if (present(devices)) then
+       if (size(devices) > 0) dev = devices(1)
+    end if
     if (c_associated(ug%handle)) call iu_destroy_grid(ug)
     call check(c_grid_from_binda(c_string(filename), scale, dev, ug%handle), "iu_read_grid")
+    if (present(devices)) then
+       if (size(devices) > 1) call check(c_grid_replicate(ug%handle, size(devices), devices), "iu_read_grid")
+    end if
     call check(c_grid_info(ug%handle, info), "iu_read_grid")
     ug%cell_type = info(1)
     ug%n_points = info(2)
@@ -405,6 +439,19 @@ contains
     if (ug%n_icell_data > 0) call check(c_download_icell_data(ug%handle, 1, &
          ug%n_icell_data, ug%icell_data), "iu_read_grid")
   end subroutine iu_read_grid
+
+  !> number of GPUs that hold a replica of the mesh
+  integer function iu_device_count(ug)
+    type(iu_grid_t), intent(in) :: ug
+    iu_device_count = c_device_count(ug%handle)
+  end function iu_device_count
+
+  !> iu_get_cell_center (:264-269) for every cell: centers(3, n_cells), the values the search uses
+  subroutine iu_get_cell_centers(ug, centers)
+    type(iu_grid_t), intent(in) :: ug
+    real(dp), intent(out)       :: centers(3, ug%n_cells)
+    call check(c_export_geometry(ug%handle, c_null_ptr, c_null_ptr, c_null_ptr, centers), "iu_get_cell_centers")
+  end subroutine iu_get_cell_centers
 
   subroutine iu_destroy_grid(ug)
     type(iu_grid_t), intent(inout) :: ug
@@ -771,3 +818,13 @@ contains
   end subroutine iu_get_cell_through_neighbors
 
 end module m_iu_b200
+
+!> The reference's module name as a thin re-export: user code keeps its `use m_interp_unstructured`
+!> line (m_interp_unstructured.f90:1) and links libiu_b200.so instead of libinterp_unstructured.a.
+!> Public procedures of the reference that are intentionally absent: iu_point_is_inside_cell,
+!> iu_reserve_*_storage, and the callback form of iu_integrate_along_field (INTEGRATION.md, section 3).
+module m_interp_unstructured
+  use m_iu_b200
+  implicit none
+  public
+end module m_interp_unstructured

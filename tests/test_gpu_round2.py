@@ -213,3 +213,93 @@ def test_two_streams_on_one_grid():
     g.check_dev()
     for k in range(2):
         assert torch.equal(ics[k], ref[k][1]) and torch.equal(outs[k], ref[k][0])
+
+
+def _multi_checks(g, o, pts, n_rep):
+    """host-buffer batch calls of a handle with n_rep replicas against the oracle and the single-GPU results"""
+    assert g.device_count == n_rep and g.stats()["devices"] == n_rep
+    lo, hi = pts.min(0), pts.max(0)
+    nq = 300_001                                           # not a multiple of the slab alignment
+    r = meshgen.uniform_queries(nq, lo - 0.02 * (hi - lo), hi + 0.02 * (hi - lo), seed=31)
+    ores, oic = o.interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -4.5), nn="brute", nthreads=NT)
+    res, ic = g.iu_interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -4.5))
+    assert (ic == oic).all() and np.array_equal(res, ores)
+    st = g.stats()
+    assert st["queries"] >= nq and st["not_found"] == int((oic < 1).sum())
+    # every replica worked on its slab
+    per = [g.replica(i).stats()["queries"] for i in range(n_rep)]
+    assert all(q > 0 for q in per[1:]) and per[0] > sum(per[1:]), per   # replica 0 = the handle: reports the sum over all
+    # fused call, cell scalars, nearest centre, walk
+    cres, ic2 = g.iu_get_cell_scalar_at(r, 1, res=np.full(nq, -2.5))
+    ocres, oic2 = o.get_cell_scalar_at(r, 1, res=np.full(nq, -2.5), nn="brute", nthreads=NT)
+    assert (ic2 == oic2).all() and np.array_equal(cres, ocres)
+    f_res, f_cres, f_ic = g.iu_interpolate_and_cell_scalar_at(r, [1, 2, 3, 4], 1, var_at_r=np.full((nq, 4), -4.5), cell_res=np.full(nq, -2.5))
+    assert (f_ic == oic2).all() and np.array_equal(f_res, ores) and np.array_equal(f_cres, ocres)
+    assert (g.find_nearby_cell_kdtree(r) == o.nearest(r, "brute", nthreads=NT)[0]).all()
+    ok = oic >= 1
+    r0 = o.cell_centers[oic[ok] - 1]
+    ic1, r_p, ns, stt = g.iu_get_cell_through_neighbors(2 ** 20, r0, r[ok] + 0.01, oic[ok])
+    oic1, or_p, ons, ostt = o.get_cell_through_neighbors(2 ** 20, r0, r[ok] + 0.01, oic[ok])
+    assert (ic1 == oic1).all() and (ns == ons).all() and (stt == ostt).all() and np.array_equal(r_p, or_p)
+    # a column update reaches every replica
+    col = np.cos(7 * pts[:, 0]) + pts[:, 1]
+    g.set_point_data(2, col)
+    o.set_point_data(2, col)
+    ores, oic = o.interpolate_at(r, [2, 1], var_at_r=np.full((nq, 2), -4.5), nn="brute", nthreads=NT)
+    res, ic = g.iu_interpolate_at(r, [2, 1], var_at_r=np.full((nq, 2), -4.5))
+    assert (ic == oic).all() and np.array_equal(res, ores)
+    # an added column too
+    iv = g.iu_add_point_data("extra")
+    g.set_point_data(iv, 2.0 * col)
+    res, ic = g.iu_interpolate_at(r, [iv], var_at_r=np.full((nq, 1), -4.5))
+    assert np.array_equal(res[oic >= 1, 0], 2.0 * ores[oic >= 1, 0])
+    # a hint above n_cells is an error on whichever device sees it (:490)
+    bad = np.zeros(nq, dtype=np.int32)
+    bad[-5] = g.n_cells + 1
+    with pytest.raises(api.IUError):
+        g.iu_interpolate_at(r, [1], i_cell=bad)
+
+
+def _multi_fixture():
+    pts, cells = meshgen.kuhn_tet_mesh(16, seed=9)
+    nb = api.build_cell_neighbors(cells, pts, "tetra")
+    pd = meshgen.smooth_fields(pts, 4)
+    cd = np.arange(1, len(cells) + 1, dtype=np.float64)
+    return pts, cells, nb, pd, cd
+
+
+def test_multi_replica_handle_on_one_gpu(monkeypatch):
+    """iu_b200_grid_replicate + the slab threads of the host-buffer calls, exercised on a single GPU: the test hook
+    IU_B200_ALLOW_SAME_DEVICE_REPLICAS puts three replicas (device-to-device clones) on device 0."""
+    monkeypatch.setenv("IU_B200_ALLOW_SAME_DEVICE_REPLICAS", "1")
+    pts, cells, nb, pd, cd = _multi_fixture()
+    g = api.Grid.from_arrays("tetra", pts, cells, nb, pd, cell_data=cd, device=0)
+    o = OracleGrid.from_arrays("tetra", pts, cells, nb, pd, cell_data=cd)
+    g.replicate([0, 0])
+    _multi_checks(g, o, pts, 3)
+    g.close()
+
+
+def test_multi_gpu_handle_two_devices():
+    """one handle, two GPUs (skipped on a one-GPU box): results identical to the oracle's and to the single-GPU handle's"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    pts, cells, nb, pd, cd = _multi_fixture()
+    g = api.Grid.from_arrays("tetra", pts, cells, nb, pd, cell_data=cd, devices=[0, 1])
+    o = OracleGrid.from_arrays("tetra", pts, cells, nb, pd, cell_data=cd)
+    assert g.replica(1).device == 1
+    _multi_checks(g, o, pts, 2)
+    # the device-buffer calls of replica 1 with tensors of GPU 1
+    dev1 = torch.device("cuda", 1)
+    r = meshgen.uniform_queries(200_000, [0.05] * 3, [0.95] * 3, seed=77)
+    with torch.cuda.device(1):
+        r_t = torch.from_numpy(r).to(dev1)
+        ic_t = torch.zeros(len(r), dtype=torch.int32, device=dev1)
+        out_t = torch.zeros((len(r), 4), dtype=torch.float64, device=dev1)
+        g1 = g.replica(1)
+        g1.iu_interpolate_at_dev(r_t, [1, 2, 3, 4], out_t, ic_t)
+        g1.check_dev()
+    res, ic = g.replica(0).iu_interpolate_at(r, [1, 2, 3, 4])
+    assert np.array_equal(ic_t.cpu().numpy(), ic) and np.array_equal(out_t.cpu().numpy(), res)
+    g.close()
