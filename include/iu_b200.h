@@ -86,6 +86,8 @@ extern "C" {
 #define IU_B200_STAT_NN_VOXEL_BUILD_US 14 /* device time of the last table build */
 #define IU_B200_STAT_DEVICES 15        /* GPUs holding a replica of the mesh (iu_b200_device_count) */
 #define IU_B200_STAT_REPLICATE_US 16   /* host time spent replicating the built mesh device to device */
+#define IU_B200_STAT_BOUNDS_ERRORS 17  /* -1 in normal builds; builds with -DIU_CHECKED=1 range-check every index the kernels
+                                        * derive from mesh / query data and count the violations here */
 #define IU_B200_N_STATS 18
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */

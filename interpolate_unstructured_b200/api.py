@@ -33,7 +33,7 @@ OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KE
 OPT_NN_VOXEL_DENSITY = 7
 STAT_NAMES = ["kernel_launches", "walk_limit_hits", "queries", "workspace_bytes", "mesh_bytes", "tree_depth",
               "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "nn_voxels", "nn_voxels_tree", "nn_voxel_entries",
-              "nn_tree_queries", "nn_voxel_build_us", "devices", "replicate_us", "reserved17"]
+              "nn_tree_queries", "nn_voxel_build_us", "devices", "replicate_us", "bounds_errors"]
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)

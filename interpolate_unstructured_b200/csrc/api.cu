@@ -965,6 +965,7 @@ int iu_b200_get_stats(iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
     stats[IU_B200_STAT_SORT_NS] = (int64_t)g->timed_ns[1];
     stats[IU_B200_STAT_DEVICES] = 1 + (int64_t)g->replicas.size();
     stats[IU_B200_STAT_REPLICATE_US] = (int64_t)(g->replicate_ms * 1e3);
+    stats[IU_B200_STAT_BOUNDS_ERRORS] = (int64_t)bounds_errors();
     // a multi-GPU handle reports the sums over its devices for the counters that add up
     for (iu_b200_grid* r : g->replicas) {
       int64_t rs[IU_B200_N_STATS];
@@ -974,6 +975,7 @@ int iu_b200_get_stats(iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
                     IU_B200_STAT_MESH_BYTES, IU_B200_STAT_NN_TREE_QUERIES, IU_B200_STAT_NOT_FOUND, IU_B200_STAT_QUERY_KERNEL_NS,
                     IU_B200_STAT_QUERY_KERNEL_LAUNCHES, IU_B200_STAT_SORT_NS})
         stats[k] += rs[k];
+      if (rs[IU_B200_STAT_BOUNDS_ERRORS] > 0) stats[IU_B200_STAT_BOUNDS_ERRORS] += rs[IU_B200_STAT_BOUNDS_ERRORS];
     }
     return (int)IU_B200_OK;
   });

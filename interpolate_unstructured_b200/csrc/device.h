@@ -157,6 +157,7 @@ int morton_end_bit(const DeviceGrid& g);
 int launch_build_voxels(const DeviceGrid& g, const VoxelGrid& v, int64_t n_vox, uint32_t* lists, unsigned long long* stats,
                         cudaStream_t s);
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s);
+long long bounds_errors();   // builds with -DIU_CHECKED=1: index-range violations seen by the kernels so far; otherwise -1
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s);
 int launch_ray_length_sample(int64_t n, int n_samples, const double* r0, const double* r1, double* sum, cudaStream_t s);
 int launch_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const double* y, double* r, cudaStream_t s);

@@ -29,6 +29,20 @@ namespace {
 
 constexpr double TINY_DISTANCE = 1e-100;   // m_interp_unstructured.f90:20
 constexpr double HUGE_DISTANCE = 1e100;    // :738
+// -DIU_CHECKED=1 (make LIBDIR=../lib_checked EXTRA=-DIU_CHECKED=1): every index the kernels derive from mesh or query
+// data (permutation entries, start / neighbour cells, leaf slots, voxel ids, point ids, original cell ids) is range
+// checked before it is used; violations are counted (IU_B200_STAT_BOUNDS_ERRORS) and the access is skipped.  This is the
+// repository's own memcheck: compute-sanitizer is closed on the GPU pool this was developed on (tools/sanitize_smoke.py).
+#ifndef IU_CHECKED
+#define IU_CHECKED 0
+#endif
+#if IU_CHECKED
+__device__ unsigned long long g_bounds_errors = 0;
+__device__ long long g_lim[4] = {0, 0, 0, 0};   // device slots, points, voxels, leaves: set before every launch
+#define IU_OOB(cond) ((cond) ? (atomicAdd(&g_bounds_errors, 1ULL), true) : false)
+#else
+#define IU_OOB(cond) false
+#endif
 #ifndef IU_QUERY_THREADS
 #define IU_QUERY_THREADS 256
 #endif
@@ -54,13 +68,46 @@ constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #ifndef IU_STREAM_HINTS
 #define IU_STREAM_HINTS 1
 #endif
+// A load that misses L2 fetches a whole 128-byte line from DRAM by default on B200 (tools/micro/gather_granularity.cu:
+// 125 bytes of DRAM reads per scattered 4-byte load); the .L2::64B qualifier halves that (63 bytes).  The scattered
+// query IO (24-byte coordinates, 4-byte hints through the sort permutation) asks for 64 bytes; IU_LTC64_MESH does the
+// same for the 32 / 64-byte gathers of the search structures and the point data.
+#ifndef IU_LTC64
+#define IU_LTC64 1
+#endif
+#ifndef IU_LTC64_MESH
+#define IU_LTC64_MESH 0
+#endif
+#if IU_LTC64
+#define IU_LTC_Q ".L2::64B"
+#else
+#define IU_LTC_Q ""
+#endif
+#if IU_LTC64_MESH
+#define IU_LTC_M ".L2::64B"
+#else
+#define IU_LTC_M ""
+#endif
 #if IU_STREAM_HINTS
-#define LD_STREAM(p) __ldcs(p)
+#define IU_CS ".cs"
 #define ST_STREAM(p, v) __stcs(p, v)
 #else
-#define LD_STREAM(p) (*(p))
+#define IU_CS ""
 #define ST_STREAM(p, v) (*(p) = (v))
 #endif
+__device__ __forceinline__ double ld_stream(const double* p) {
+  double v; asm volatile("ld.global" IU_CS IU_LTC_Q ".f64 %0, [%1];" : "=d"(v) : "l"(p)); return v;
+}
+__device__ __forceinline__ double2 ld_stream(const double2* p) {
+  double2 v; asm volatile("ld.global" IU_CS IU_LTC_Q ".v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p)); return v;
+}
+__device__ __forceinline__ int ld_stream(const int* p) {
+  int v; asm volatile("ld.global" IU_CS IU_LTC_Q ".b32 %0, [%1];" : "=r"(v) : "l"(p)); return v;
+}
+__device__ __forceinline__ uint32_t ld_stream(const uint32_t* p) {
+  uint32_t v; asm volatile("ld.global" IU_CS IU_LTC_Q ".b32 %0, [%1];" : "=r"(v) : "l"(p)); return v;
+}
+#define LD_STREAM(p) ld_stream(p)
 
 struct V3 { double x, y, z; };
 __device__ __forceinline__ V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
@@ -106,7 +153,12 @@ __device__ __forceinline__ V3 ld3(const double* p) { return {__ldg(p), __ldg(p +
 struct D4 { double x, y, z, w; };
 __device__ __forceinline__ D4 ld256(const double* p) {
   D4 r;
-  asm volatile("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+  asm volatile("ld.global.nc" IU_LTC_M ".v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 ld128u(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc" IU_LTC_M ".v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
   return r;
 }
 // 4 consecutive (x, y, z) triples at a 32-byte aligned address as three 32-byte loads
@@ -463,6 +515,7 @@ __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx
   // two batches of four slots: x, y, z of four centres = three independent 32-byte loads.  The
   // common path is branch-free (min / select); exact ties only raise a flag and are sorted out below.
   const int base = (node - t.n_internal) * LEAF;
+  if (IU_OOB(node < t.n_internal || node - t.n_internal >= g_lim[3])) return;
   const double* c = t.centers4 + 3 * (size_t)base;
   bool tie = false;
 #pragma unroll
@@ -501,7 +554,7 @@ __device__ __forceinline__ void scan_leaf(const TreeView& t, int node, double qx
 // centre can fall below the exact one, so no centre at a distance <= best (ties included) is dropped.
 __device__ __forceinline__ float box_lower_bound(const float* b, double qx, double qy, double qz) {
   float lx, ly, lz, hx, hy, hz, p0, p1;
-  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+  asm volatile("ld.global.nc" IU_LTC_M ".v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=f"(lx), "=f"(ly), "=f"(lz), "=f"(hx), "=f"(hy), "=f"(hz), "=f"(p0), "=f"(p1) : "l"(b));
   const float ox = fmaxf(fmaxf(__fsub_rd(lx, __double2float_ru(qx)), __fsub_rd(__double2float_rd(qx), hx)), 0.0f);
   const float oy = fmaxf(fmaxf(__fsub_rd(ly, __double2float_ru(qy)), __fsub_rd(__double2float_rd(qy), hy)), 0.0f);
@@ -768,14 +821,16 @@ __device__ __forceinline__ int nn_voxel(const VoxelGrid& V, const double* __rest
   }
   if (!ok) return -2;
   const size_t vox = ((size_t)(int)tz * V.n[1] + (size_t)(int)ty) * V.n[0] + (size_t)(int)tx;
+  if (IU_OOB((long long)vox >= g_lim[2])) return -2;
   const uint4* L = reinterpret_cast<const uint4*>(V.lists) + vox * (VOX_K / 4);
   double best = __longlong_as_double(0x7ff0000000000000LL);
   int besti = -2, besto = 0x7fffffff;
 #pragma unroll 1
   for (int g = 0; g < VOX_K / 4; ++g) {
-    const uint4 e = __ldg(L + g);
+    const uint4 e = ld128u(L + g);
     if (e.x >= VOX_TREE) break;   // VOX_END: list complete; VOX_TREE (first group only): besti stays -2
     const uint32_t sl[4] = {e.x, e.y, e.z, e.w};
+    if (IU_OOB((long long)e.x >= g_lim[0] || (long long)e.y >= g_lim[0] || (long long)e.z >= g_lim[0] || (long long)e.w >= g_lim[0])) break;
     D4 c[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) c[j] = ld256(cen32 + 4 * (size_t)sl[j]);
@@ -811,6 +866,7 @@ __device__ __forceinline__ void walk_ray(const double* __restrict__ rec, V3 r0, 
   int mask0 = 0;
   if (mask) mask0 = __ldg(mask + (__ldg(reinterpret_cast<const int32_t*>(rec + (size_t)(ic0 - 1) * L::STRIDE) + L::ORG_I) - 1));
   for (n_steps = 1; n_steps <= max_steps; ++n_steps) {
+    if (IU_OOB(ic1 < 1 || ic1 > g_lim[0])) { status = -1; ic1 = 0; break; }
     const double* R = rec + (size_t)(ic1 - 1) * L::STRIDE;
     double face_distance = HUGE_DISTANCE;
     int i_face = -1;
@@ -975,6 +1031,7 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
   constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
   using L = RecLayout<PPC>;
   int ic = start;
+  if (IU_OOB(start < 1 || start > g_lim[0])) return;
   if (MODE != QM_INTERP_ICELL) {
     const D4 c0 = ld256(P.cen32 + 4 * (size_t)(start - 1));
     const V3 r0{c0.x, c0.y, c0.z};                                                    // :429
@@ -1002,6 +1059,8 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
     pid[0] = c.x; pid[1] = c.y; pid[2] = c.z; pid[3] = c.w;
     vol = __ldg(R + L::VOL);
   }
+  if (IU_OOB(orig < 1 || orig > P.n_cells || pid[0] < 0 || pid[0] >= g_lim[1] || pid[1] < 0 || pid[1] >= g_lim[1] ||
+             pid[2] < 0 || pid[2] >= g_lim[1] || (PPC == 4 && (pid[3] < 0 || pid[3] >= g_lim[1])))) return;
   if (MODE != QM_INTERP_ICELL && MODE != QM_INTERP_CELL) ST_STREAM(P.i_cell + i, orig);
   if (MODE == QM_CELL_F64) {
     ST_STREAM(P.out_f64 + i, __ldg(P.cd + (size_t)P.ivars[0] * P.n_cells + (orig - 1)));          // :447
@@ -1123,6 +1182,7 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
     } else if (t >= P.n) break;
     const uint32_t pe = P.perm ? LD_STREAM(P.perm + t) : 0u;
     const int64_t i = P.perm ? (int64_t)(pe & ~PERM_HINT_BIT) : t;
+    if (IU_OOB(i < 0 || i >= P.n)) continue;
     // a query's 24 bytes as two scattered loads instead of three: 16 + 8 or 8 + 16 bytes, whichever is aligned
     double qx, qy, qz;
     {
@@ -1165,6 +1225,7 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_walk(const double* __restrict
                                                         int n_cells, unsigned long long* counters, WalkArgs a) {
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < a.n; t += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = a.perm ? (int64_t)LD_STREAM(a.perm + t) : t;
+    if (IU_OOB(i < 0 || i >= a.n)) continue;
     const int h = a.ic0[i];
     if (h < 1 || h > n_cells) { atomicAdd(counters + CNT_HINT_ERROR, 1ULL); continue; }
     const V3 r0 = ld3(a.r0 + 3 * i), r1 = ld3(a.r1 + 3 * i);
@@ -1209,6 +1270,7 @@ __global__ void __launch_bounds__(128) k_trace(const double* __restrict__ rec, c
   if (t >= a.n) return;
   // neighbouring threads trace neighbouring lines: their walks read the same records
   const int64_t i = a.perm ? (int64_t)a.perm[t] : t;
+  if (IU_OOB(i < 0 || i >= a.n)) return;
   const int ndim = a.ndim, nvar = a.nvar, nt = ndim + nvar;
   double* Y = a.y + (size_t)i * nt * a.max_steps;
   double* YF = a.y_field ? a.y_field + (size_t)i * ndim * a.max_steps : nullptr;
@@ -1541,8 +1603,30 @@ int launch_build_voxels(const DeviceGrid& g, const VoxelGrid& v, int64_t n_vox, 
   return 1;
 }
 
+// checked builds: the index limits of this grid for the kernels about to be launched on s
+static void set_check_limits(const DeviceGrid& g, cudaStream_t s) {
+#if IU_CHECKED
+  const long long lim[4] = {(long long)g.n_leaves * LEAF, g.n_points, (long long)g.n_vox, g.n_leaves};
+  cudaMemcpyToSymbolAsync(g_lim, lim, sizeof(lim), 0, cudaMemcpyHostToDevice, s);
+#else
+  (void)g; (void)s;
+#endif
+}
+
+long long bounds_errors() {
+#if IU_CHECKED
+  unsigned long long v = 0;
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(&v, g_bounds_errors, sizeof(v));
+  return (long long)v;
+#else
+  return -1;
+#endif
+}
+
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
+  set_check_limits(g, s);
   QueryKernelParams P;
   P.tree = TreeView{g.fat, g.centers4, g.orig_of_dev, g.box, g.n_internal};
   P.vox = g.vox; P.cen32 = g.cen32;
@@ -1579,6 +1663,7 @@ int launch_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const double*
 
 int launch_trace(const DeviceGrid& g, const TraceArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
+  set_check_limits(g, s);
   const int b = blocks_for(a.n, 128);
   if (g.cell_type == IU_TRIANGLE_CT)
     k_trace<IU_TRIANGLE_CT><<<b, 128, 0, s>>>(g.rec, g.dev_of_orig, g.pd, g.pd_stride, g.icd, g.n_cells, g.counters, a);
@@ -1612,6 +1697,7 @@ int launch_ray_length_sample(int64_t n, int n_samples, const double* r0, const d
 
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s) {
   if (a.n == 0) return 0;
+  set_check_limits(g, s);
   const int32_t* mask = a.mask_col >= 0 ? g.icd + (size_t)a.mask_col * g.n_cells : nullptr;
   const int64_t need = (a.n + QUERY_THREADS - 1) / QUERY_THREADS;
   const int b = (int)(need < sm_count() * 8 ? need : sm_count() * 8);

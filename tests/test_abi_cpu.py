@@ -107,3 +107,25 @@ def test_large_neighbor_build_parallel_path(lib):
     ref = meshgen.cell_neighbors(cells, pts, "tetra")
     assert (ref == got).all()
     assert (got < 0).sum() == 6 * 2 * 26 * 26                       # boundary faces of the cube
+
+
+def test_header_is_plain_c99_and_c_driver_fails_loudly_without_a_gpu(tmp_path):
+    """include/iu_b200.h must be usable from C (no C++-isms); the C driver of tests/c_driver links against the library
+    and, on a machine without a GPU, stops with the library's 'no CPU fallback' error instead of computing anything."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    probe = tmp_path / "probe.c"
+    probe.write_text('#include "iu_b200.h"\nint main(void) { return iu_b200_version() < 0; }\n')
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-fsyntax-only", "-I", os.path.join(root, "include"), str(probe)], check=True)
+    import __graft_entry__ as ge
+    exe = ge.build_c_driver()
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except ImportError:
+        has_gpu = False
+    out = subprocess.run([exe, os.path.join(root, "tests", "golden")], capture_output=True, text=True)
+    if has_gpu:
+        assert out.returncode == 0 and "PASSED" in out.stdout, out.stderr
+    else:
+        assert out.returncode != 0 and "no CPU fallback" in out.stderr

@@ -303,3 +303,15 @@ def test_multi_gpu_handle_two_devices():
     res, ic = g.replica(0).iu_interpolate_at(r, [1, 2, 3, 4])
     assert np.array_equal(ic_t.cpu().numpy(), ic) and np.array_equal(out_t.cpu().numpy(), res)
     g.close()
+
+
+def test_plain_c_driver_runs_the_reference_test_programs():
+    """tests/c_driver/iu_driver.c: test_triangle / test_quad / test_tetra (1e-14 on the linear field, one point per call
+    like the reference's loops) and benchmark.f90's two passes, through the C ABI from plain C."""
+    import subprocess
+    import __graft_entry__ as ge
+    exe = ge.build_c_driver()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([exe, os.path.join(root, "tests", "golden")], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.count("PASSED") == 5

@@ -5,7 +5,11 @@ kd-tree fallback), cell scalars, the fused call, ray batches with a mask, the fi
 geometry / mesh export and a two-replica handle.  Results are checked against the oracle so that a silent corruption
 fails the run as well.
 
-    compute-sanitizer --tool memcheck python tools/sanitize_smoke.py"""
+    compute-sanitizer --tool memcheck python tools/sanitize_smoke.py
+    IU_B200_LIB=$PWD/interpolate_unstructured_b200/lib_checked/libiu_b200.so python tools/sanitize_smoke.py
+
+The second form is what this pool allows (compute-sanitizer is closed on it): the library built with -DIU_CHECKED=1
+range-checks every index its kernels derive from mesh or query data and counts violations (IU_B200_STAT_BOUNDS_ERRORS)."""
 import os
 import sys
 
@@ -83,8 +87,10 @@ def main():
         g.replicate([0])
         res, ic = g.iu_interpolate_at(np.tile(r, (5, 1)), [1, 2])
         assert g.device_count == 2 and (ic[:nq] == ic[nq:2 * nq]).all()
+        be = g.stats()["bounds_errors"]
+        assert be <= 0, f"{be} index-range violations counted by the checked build"
         g.close()
-        print(kind, "ok", flush=True)
+        print(kind, "ok", "(checked build: 0 index-range violations)" if be == 0 else "(unchecked build)", flush=True)
     print("sanitize smoke ok")
 
 
