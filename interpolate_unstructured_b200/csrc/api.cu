@@ -914,7 +914,7 @@ static int set_option_one(iu_b200_grid* g, int option, int64_t value) {
       g->dev_batch = value;
       return IU_B200_OK;
     case IU_B200_OPT_DYNAMIC_TILES:
-      if (value < 0 || value > 1) break;
+      if (value < 0 || value > 2) break;
       g->dynamic_tiles = (int)value;
       return IU_B200_OK;
     case IU_B200_OPT_TIME_KERNELS:

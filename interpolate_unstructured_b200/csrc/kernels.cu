@@ -1012,6 +1012,14 @@ struct QueryKernelParams {
   int ivars[MAX_VARS];
 };
 
+// the kd-tree search as a real call: with a voxel table it serves 0.2 % of the queries, and inlined its registers
+// would be charged to every query of the lane-refill kernel
+__device__ __noinline__ int nearest_center_call(const double* fat, const double* centers4, const int32_t* orig_of_dev,
+                                                const float* box, int n_internal, float* s_lb, double qx, double qy, double qz) {
+  const TreeView t{fat, centers4, orig_of_dev, box, n_internal};
+  return nearest_center(t, s_lb, qx, qy, qz);
+}
+
 // find_nearby_cell_kdtree (:272-288): the voxel table where it applies, else the kd-tree search
 __device__ __forceinline__ int nearest_slot(const QueryKernelParams& P, float* s_lb, double qx, double qy, double qz) {
   int slot = -2;
@@ -1022,14 +1030,25 @@ __device__ __forceinline__ int nearest_slot(const QueryKernelParams& P, float* s
   }
   return slot;
 }
+__device__ __forceinline__ int nearest_slot_call(const QueryKernelParams& P, float* s_lb, double qx, double qy, double qz) {
+  int slot = -2;
+  if (P.vox.lists) slot = nn_voxel(P.vox, P.cen32, qx, qy, qz);
+  if (slot == -2) {
+    if (P.vox.lists) atomicAdd(P.counters + CNT_NN_TREE, 1ULL);
+    slot = nearest_center_call(P.tree.fat, P.tree.centers4, P.tree.orig_of_dev, P.tree.box, P.tree.n_internal, s_lb, qx, qy, qz);
+  }
+  return slot;
+}
 
 // Everything after the start cell is known: ray walk from the start cell's centre (iu_get_cell,
 // :429-432), then the mode's output.  `start` is a 1-based device id; for QM_INTERP_ICELL it is the
 // containing cell itself (no walk).
 template <int CT, int MODE, int NV>
+__device__ __forceinline__ void emit_result(const QueryKernelParams& P, int64_t i, double qx, double qy, double qz, int ic);
+
+template <int CT, int MODE, int NV>
 __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t i, double qx, double qy, double qz, int start) {
   constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
-  using L = RecLayout<PPC>;
   int ic = start;
   if (IU_OOB(start < 1 || start > g_lim[0])) return;
   if (MODE != QM_INTERP_ICELL) {
@@ -1041,8 +1060,16 @@ __device__ __forceinline__ void finish_query(const QueryKernelParams& P, int64_t
       ic = IU_WALK_LIMIT;
       atomicAdd(P.counters + CNT_WALK_LIMIT, 1ULL);
     }
-    if (ic < 1) { ST_STREAM(P.i_cell + i, ic); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); return; }   // :492
   }
+  emit_result<CT, MODE, NV>(P, i, qx, qy, qz, ic);
+}
+
+// The walk has ended in device cell ic (1-based; < 1: left the domain / step cap): the mode's outputs.
+template <int CT, int MODE, int NV>
+__device__ __forceinline__ void emit_result(const QueryKernelParams& P, int64_t i, double qx, double qy, double qz, int ic) {
+  constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
+  using L = RecLayout<PPC>;
+  if (MODE != QM_INTERP_ICELL && ic < 1) { ST_STREAM(P.i_cell + i, ic); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); return; }   // :492
   const double* R = P.rec + (size_t)(ic - 1) * L::STRIDE;
   const int32_t* RI = reinterpret_cast<const int32_t*>(R);
   int orig, pid[4];
@@ -1216,6 +1243,142 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
       start = __ldg(P.dev_of_orig + h);                                                // :424-426
     }
     finish_query<CT, MODE, NV>(P, i, qx, qy, qz, start);
+  }
+}
+
+// One iteration of the loop at :698-723 for the lane-refill kernel below: the statements of walk_ray's loop body.
+// Returns true while the walk continues (ic1 = the next cell); false when it has ended: ic1 = the containing cell,
+// or < 1 where the ray left the domain, or IU_WALK_LIMIT (counted) after max_steps iterations.
+template <int PPC>
+struct WalkLane { V3 u, r_p; double distance_left; int ic1, n_steps; };
+
+template <int PPC>
+__device__ __forceinline__ bool walk_step(const QueryKernelParams& P, WalkLane<PPC>& w) {
+  using L = RecLayout<PPC>;
+  if (IU_OOB(w.ic1 < 1 || w.ic1 > g_lim[0])) { w.ic1 = 0; return false; }
+  const double* R = P.rec + (size_t)(w.ic1 - 1) * L::STRIDE;
+  double face_distance = HUGE_DISTANCE;
+  int i_face = -1;
+  if (PPC == 4) {
+#pragma unroll
+    for (int h = 0; h < 4; h += 2) {
+      V3 fn[2], rf[2];
+      ld3n<2>(R + L::NRM + 3 * h, fn);
+      ld3n<2>(R + L::PTS + 3 * h, rf);
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const double pdn = dot3(w.u, fn[j]);
+        const double dist = dot3(rf[j] - w.r_p, fn[j]) / pdn;
+        if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = h + j; }
+      }
+    }
+  } else {
+    V3 fn[3], rf[3];
+    ld3n<3>(R + L::NRM, fn);
+    ld3n<3>(R + L::PTS, rf);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double pdn = dot3(w.u, fn[k]);
+      const double dist = dot3(rf[k] - w.r_p, fn[k]) / pdn;
+      if (pdn > 0 && dist < face_distance) { face_distance = dist; i_face = k; }
+    }
+  }
+  w.r_p = {w.r_p.x + face_distance * w.u.x, w.r_p.y + face_distance * w.u.y, w.r_p.z + face_distance * w.u.z};   // :762
+  w.distance_left = w.distance_left - face_distance;
+  if (!(w.distance_left > 0)) return false;                                            // found, :720-721
+  w.ic1 = __ldg(reinterpret_cast<const int32_t*>(R) + L::NBR_I + i_face);
+  if (w.ic1 < 1) return false;                                                         // left the domain, :706-709
+  if (++w.n_steps > P.max_steps) { w.ic1 = IU_WALK_LIMIT; atomicAdd(P.counters + CNT_WALK_LIMIT, 1ULL); return false; }
+  return true;
+}
+
+// k_query with LANE REFILL (sorted batches, the modes that walk): a warp draws tiles of STILE consecutive sorted queries
+// like k_query<.., SCHED = 1>, but a lane takes the next query of the tile as soon as its own walk has ended.  Every pass
+// of the loop = [idle lanes: read the query, nearest centre / hint, set up the ray] + [all lanes: ONE walk step] +
+// [lanes whose walk ended: outputs].  A warp of k_query runs ~3.3 walk iterations per 32 queries because some lane always
+// needs one more (mean 1.3 per query, 25 % of the lanes in the second iteration, 4 % in the third); here every walk
+// step runs with (nearly) all lanes.  Same statements per query in the same order: results are bit-identical.
+template <int CT, int MODE, int NV>
+__global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query_refill(const QueryKernelParams P) {
+  extern __shared__ float s_lb[];
+  constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;
+  constexpr int STILE = IU_STILE;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  int64_t tile = 0;
+  int tile_pos = STILE;         // queries of the current tile already handed out (STILE: draw a new tile)
+  bool more = true, busy = false;
+  int64_t i = 0;
+  double qx = 0, qy = 0, qz = 0;
+  WalkLane<PPC> w;
+  w.u = w.r_p = V3{0, 0, 0}; w.distance_left = 0; w.ic1 = 0; w.n_steps = 0;
+  for (;;) {
+    const unsigned idle = __ballot_sync(0xffffffffu, !busy);
+    if (idle && more) {
+      if (tile_pos >= STILE) {
+        unsigned long long b = 0;
+        if (lane == 0) b = atomicAdd(P.ticket, (unsigned long long)STILE);
+        tile = (int64_t)__shfl_sync(0xffffffffu, b, 0);
+        tile_pos = 0;
+        if (tile >= P.n) more = false;
+      }
+      if (more) {
+        const int64_t left = P.n - tile;
+        const int avail = (int)(left < STILE ? left : STILE) - tile_pos;
+        const int rank = __popc(idle & lt);
+        const bool take = !busy && rank < avail;
+        const int n_idle = __popc(idle);
+        const int64_t t = tile + tile_pos + rank;
+        tile_pos += n_idle < avail ? n_idle : avail;
+        if (avail <= n_idle) tile_pos = STILE;
+        if (take) {
+          const uint32_t pe = P.perm ? LD_STREAM(P.perm + t) : 0u;
+          i = P.perm ? (int64_t)(pe & ~PERM_HINT_BIT) : t;
+          bool ok = !IU_OOB(i < 0 || i >= P.n);
+          if (ok) {
+            const double* rp = P.r + 3 * i;
+            if ((reinterpret_cast<uintptr_t>(rp) & 15) == 0) {
+              const double2 a = LD_STREAM(reinterpret_cast<const double2*>(rp));
+              qx = a.x; qy = a.y; qz = LD_STREAM(rp + 2);
+            } else {
+              qx = LD_STREAM(rp);
+              const double2 b = LD_STREAM(reinterpret_cast<const double2*>(rp + 1));
+              qy = b.x; qz = b.y;
+            }
+            const int h = !P.perm || (pe & PERM_HINT_BIT) ? LD_STREAM(P.i_cell + i) : 0;
+            int start = 0;
+            if (h > P.n_cells) { atomicAdd(P.counters + CNT_HINT_ERROR, 1ULL); ok = false; }     // error stop, :490
+            else if (h < 1) {                                                                    // :422-423
+              const int slot = nearest_slot_call(P, s_lb, qx, qy, qz);
+              if (slot < 0) { ST_STREAM(P.i_cell + i, 0); atomicAdd(P.counters + CNT_NOT_FOUND, 1ULL); ok = false; }
+              start = slot + 1;
+            } else start = __ldg(P.dev_of_orig + h);                                             // :424-426
+            if (ok && IU_OOB(start < 1 || start > g_lim[0])) ok = false;
+            if (ok) {
+              const D4 c0 = ld256(P.cen32 + 4 * (size_t)(start - 1));
+              const V3 dvec = V3{qx, qy, qz} - V3{c0.x, c0.y, c0.z};                            // r0 = the cell centre, :429
+              w.distance_left = norm2_3(dvec);
+              w.ic1 = start;
+              if (w.distance_left < TINY_DISTANCE) emit_result<CT, MODE, NV>(P, i, qx, qy, qz, start);   // :689-692
+              else {
+                w.u = V3{dvec.x / w.distance_left, dvec.y / w.distance_left, dvec.z / w.distance_left};  // :694
+                w.r_p = V3{c0.x, c0.y, c0.z};
+                w.n_steps = 1;
+                busy = true;
+              }
+            }
+          }
+        }
+      }
+    }
+    if (!__any_sync(0xffffffffu, busy)) {
+      if (!more) break;
+      continue;
+    }
+    if (busy && !walk_step<PPC>(P, w)) {
+      emit_result<CT, MODE, NV>(P, i, qx, qy, qz, w.ic1);
+      busy = false;
+    }
   }
 }
 
@@ -1425,9 +1588,30 @@ void launch_query_static(const QueryKernelParams& P, int depth, cudaStream_t s) 
   k_query<CT, MODE, NV, SCHED><<<g, QUERY_THREADS, dyn, s>>>(P);
 }
 
-// sched: 0 static grid-stride, 1 ticket tiles (sorted batches)
+template <int CT, int MODE, int NV>
+void launch_query_refill(const QueryKernelParams& P, int depth, cudaStream_t s) {
+  const size_t dyn = (size_t)(depth > 0 ? depth : 1) * QUERY_THREADS * sizeof(float);
+  static int blocks = 0;
+  static size_t blocks_dyn = ~(size_t)0;
+  if (blocks == 0 || blocks_dyn != dyn) {
+    if (dyn + 20 * 1024 > 48 * 1024)
+      cudaFuncSetAttribute((const void*)k_query_refill<CT, MODE, NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+    blocks = query_grid_blocks((const void*)k_query_refill<CT, MODE, NV>, dyn);
+    blocks_dyn = dyn;
+  }
+  const int64_t need = (P.n + QUERY_THREADS - 1) / QUERY_THREADS;
+  const int g = (int)(need < blocks ? need : blocks);
+  cudaMemsetAsync(P.ticket, 0, sizeof(unsigned long long), s);
+  k_query_refill<CT, MODE, NV><<<g, QUERY_THREADS, dyn, s>>>(P);
+}
+
+// sched: 0 static grid-stride, 1 ticket tiles (sorted batches), 2 ticket tiles with lane refill (the modes that walk)
 template <int CT, int MODE, int NV>
 void launch_query_inst(const QueryKernelParams& P, int depth, cudaStream_t s) {
+  constexpr bool walks = MODE == QM_CELL || MODE == QM_INTERP || MODE == QM_CELL_F64 || MODE == QM_CELL_I32 || MODE == QM_INTERP_CELL;
+  if constexpr (walks) {
+    if (P.ticket && P.sched == 2) { launch_query_refill<CT, MODE, NV>(P, depth, s); return; }
+  }
   if (P.ticket && P.sched >= 1) launch_query_static<CT, MODE, NV, 1>(P, depth, s);
   else launch_query_static<CT, MODE, NV, 0>(P, depth, s);
 }
