@@ -516,6 +516,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     d.points = d_points.take();
     d_cells.release(); d_neigh.release(); d_centers.release();
     if (const char* env = std::getenv("IU_B200_NN_VOXEL_DENSITY")) g->voxel_density = std::max(0, std::atoi(env));
+    if (const char* env = std::getenv("IU_B200_DYNAMIC_TILES")) g->dynamic_tiles = std::min(2, std::max(0, std::atoi(env)));   // A/B knob
     if (const char* env = std::getenv("IU_B200_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(env));   // experiment knob
     build_voxel_table(g);
     // data tables

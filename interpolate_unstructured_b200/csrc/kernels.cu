@@ -1169,13 +1169,18 @@ __device__ __forceinline__ void emit_result(const QueryKernelParams& P, int64_t 
   }
 }
 
-// THE hot kernel.  Persistent CTAs (grid = SMs x resident CTAs); the top tree levels live in
-// shared memory; one query per thread, processed in Morton order through `perm`.
+// THE hot kernel.  Persistent CTAs (grid = SMs x resident CTAs); one query per thread, processed in curve order through
+// `perm`; the dynamic shared memory holds the per-thread plane bounds of the kd-tree search (nearest_center), which only
+// the queries without a voxel list run.
 // SCHED = 0: static grid-stride assignment (unsorted batches).  SCHED = 1 (sorted batches): every
 // warp draws tiles of 128 consecutive sorted queries from a global ticket counter, so that all
 // queries in flight on the GPU stay within one narrow window of the Morton order whatever the
 // speed differences between warps and SMs.
-// Two designs that were built, measured on B200 and dropped (profiles/README.md): a three-phase
+// A walk whose FIRST iteration reads precomputed numerators (p_k - centre) . n_k instead of the start cell's vertices
+// (8 loads from one line instead of 12 from two, bit-identical) was built and dropped: the vertices are needed by the
+// interpolation anyway and 77 % of the queries end in their start cell, so the loads only moved (7.76 vs 7.57 ms,
+// profiles/experiments/r02j_first_step_precomputed.txt).
+// Designs that were built, measured on B200 and dropped (profiles/README.md): a three-phase
 // tiled kernel with a lane queue for the backtracking phase (fewer instructions, but the lost
 // intra-warp locality costs more L1 wavefronts than it saves), and a warp-packet kd-tree search
 // (uniform 32-byte loads still pay 8 LSU data-pipe wavefronts each for register write-back); and a

@@ -1,0 +1,18 @@
+#!/bin/bash
+# r02i: lane-refill kernel (IU_B200_OPT_DYNAMIC_TILES = 2) against the ticket-tile kernel (1): parity, then timing + counters
+mkdir -p gpurun_out
+B="python bench.py --queries 2e8 --steps 3 --warmup 3 --no-cpu --no-e2e"
+P="python bench.py --queries 2e8 --steps 1 --warmup 1 --no-cpu --no-e2e"
+M=dram__bytes_read.sum,dram__bytes_write.sum,lts__t_sector_hit_rate.pct,l1tex__t_sector_hit_rate.pct,gpu__time_duration.sum,smsp__thread_inst_executed_per_inst_executed.ratio,smsp__inst_executed.sum,l1tex__throughput.avg.pct_of_peak_sustained_elapsed
+show() { python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); r=d['roofline']
+print('value %.3e q/s  kernel %.2f ms/launch  share %.2f sort %.2f  ms/step %.2f'%(d['value'], r['kernel_ms_per_launch'], r['kernel_share_of_step'], r['sort_share_of_step'], d['ms_per_step']), d['checks'])"; }
+ncu1() { $P $2 > /dev/null 2>&1 && ncu --metrics $M --clock-control none -k regex:k_query -s 3 -c 1 --csv --log-file gpurun_out/r02i_$1.csv $P $2 > /dev/null 2>&1
+  grep -E "dram__|hit_rate|time_duration|inst_executed|throughput" gpurun_out/r02i_$1.csv | awk -F'","' '{print "   ", $(NF-2), $(NF-1), $NF}'; }
+{
+for dyn in 1 2; do
+  echo "== dynamic $dyn"; $B --dynamic $dyn | show; ncu1 dyn$dyn "--dynamic $dyn"
+done
+echo "== parity of the refill kernel (IU_B200_DYNAMIC_TILES=2)"; IU_B200_DYNAMIC_TILES=2 timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_round2.py -m gpu -x -q 2>&1 | tail -3
+} 2>&1 | tee gpurun_out/r02i.txt
