@@ -1012,9 +1012,9 @@ struct QueryKernelParams {
   int ivars[MAX_VARS];
 };
 
-// the kd-tree search as a real call: with a voxel table it serves 0.2 % of the queries, and inlined its registers
-// would be charged to every query of the lane-refill kernel
-__device__ __noinline__ int nearest_center_call(const double* fat, const double* centers4, const int32_t* orig_of_dev,
+// the kd-tree search behind one more function boundary for the lane-refill kernel (marking it __noinline__ crashes
+// nvcc 12.9's front end on this file, so it is an ordinary inlinable function)
+__device__ int nearest_center_call(const double* fat, const double* centers4, const int32_t* orig_of_dev,
                                                 const float* box, int n_internal, float* s_lb, double qx, double qy, double qz) {
   const TreeView t{fat, centers4, orig_of_dev, box, n_internal};
   return nearest_center(t, s_lb, qx, qy, qz);
