@@ -61,12 +61,18 @@ extern "C" {
 #define IU_B200_OPT_DEV_BATCH 4     /* max queries per internal device sub-batch (workspace bound) */
 #define IU_B200_OPT_TIME_KERNELS 5  /* 1: bracket the hot kernel and the sort with CUDA events (stats 7..9) */
 #define IU_B200_OPT_DYNAMIC_TILES 6 /* 1 (default): sorted batches are handed to warps as tiles of consecutive
-                                       queries from a device ticket counter; 0: static grid-stride assignment */
+                                       queries from a device ticket counter; 0: static grid-stride assignment;
+                                       2: ticket tiles with lane refill (measured slower, kept for A/B) */
 
 #define IU_B200_OPT_NN_VOXEL_DENSITY 7 /* voxels of the nearest-centre table per 100 cells (default 400; 0 = no table,
                                        every cold query searches the kd-tree).  The table lists, per voxel of a regular
                                        grid over the mesh's bounding box, every centre that can be nearest to a point of
                                        the voxel; results are identical with and without it.  Setting it rebuilds the table. */
+
+#define IU_B200_OPT_OVERLAP_SORT 8   /* 1 (default 0: measured, no gain): in a device batch of several sub-batches the curve keys + radix sort
+                                       of sub-batch k+1 run on a second stream beside the query kernel of sub-batch k */
+#define IU_B200_OPT_TILES_PER_WARP 9 /* tiles a warp of the query kernel processes before it retires while a sort runs
+                                       beside it (default 8); short-lived CTAs are what lets the two kernels share SMs */
 
 /* indices into the int64 array filled by iu_b200_get_stats */
 #define IU_B200_STAT_KERNEL_LAUNCHES 0 /* kernels of this library launched since creation/reset */
@@ -88,7 +94,9 @@ extern "C" {
 #define IU_B200_STAT_REPLICATE_US 16   /* host time spent replicating the built mesh device to device */
 #define IU_B200_STAT_BOUNDS_ERRORS 17  /* -1 in normal builds; builds with -DIU_CHECKED=1 range-check every index the kernels
                                         * derive from mesh / query data and count the violations here */
-#define IU_B200_N_STATS 18
+#define IU_B200_STAT_H2D_SKIPPED_BYTES 18 /* host API: bytes of i_cell NOT uploaded because a whole pipeline chunk carried no
+                                           * hint (the device buffer is zeroed instead) */
+#define IU_B200_N_STATS 20
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */
 

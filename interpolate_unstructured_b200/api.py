@@ -30,10 +30,10 @@ CELL_TYPES = {"triangle": TRIANGLE, "quad": QUAD, "tetra": TETRA}
 E_INVAL, E_CUDA, E_IO, E_HINT, E_NOMEM = -1, -2, -3, -4, -5
 CELL_WALK_LIMIT = -2
 OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KERNELS, OPT_DYNAMIC_TILES = 1, 2, 3, 4, 5, 6
-OPT_NN_VOXEL_DENSITY = 7
+OPT_NN_VOXEL_DENSITY, OPT_OVERLAP_SORT, OPT_TILES_PER_WARP = 7, 8, 9
 STAT_NAMES = ["kernel_launches", "walk_limit_hits", "queries", "workspace_bytes", "mesh_bytes", "tree_depth",
               "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "nn_voxels", "nn_voxels_tree", "nn_voxel_entries",
-              "nn_tree_queries", "nn_voxel_build_us", "devices", "replicate_us", "bounds_errors"]
+              "nn_tree_queries", "nn_voxel_build_us", "devices", "replicate_us", "bounds_errors", "h2d_skipped_bytes", "reserved19"]
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)

@@ -103,6 +103,14 @@ struct iu_b200_grid {
   // sort workspace (device API and host pipeline share it: all compute is stream-ordered by the caller)
   DevBuf<uint32_t> keys, keys_alt, idx, idx_alt;
   DevBuf<char> sort_temp;
+  // sort of sub-batch k+1 beside k_query of sub-batch k (run_query): second permutation buffer, a high-priority stream
+  // for the sorts and the events that order the two streams
+  DevBuf<uint32_t> idx_alt2;
+  cudaStream_t s_sort = nullptr;
+  cudaEvent_t ev_enter = nullptr, ev_sorted[2] = {nullptr, nullptr}, ev_queried[2] = {nullptr, nullptr};
+  size_t h2d_skipped_bytes = 0;   // i_cell uploads replaced by a device memset (all-cold chunks of the host API)
+  int overlap_sort = 0;        // IU_B200_OPT_OVERLAP_SORT (measured: no gain, profiles/experiments/r02k_sort_overlap.txt)
+  int tiles_per_warp = 8;      // k_query warps retire after this many tiles while a sort runs beside them
   // ray-walk sort decision (IU_B200_OPT_SORT_QUERIES = 2): mean sampled ray length of the latest measured call
   DevBuf<double> walk_sum;
   double* h_walk_sum = nullptr;   // pinned
@@ -152,7 +160,7 @@ struct DeviceGuard {
 };
 
 size_t workspace_bytes(const iu_b200_grid* g) {
-  size_t b = (g->keys.n + g->keys_alt.n + g->idx.n + g->idx_alt.n) * 4 + g->sort_temp.n + g->h_stage_bytes;
+  size_t b = (g->keys.n + g->keys_alt.n + g->idx.n + g->idx_alt.n + g->idx_alt2.n) * 4 + g->sort_temp.n + g->h_stage_bytes;
   for (const Slot& s : g->slot)
     b += (s.r.n + s.r1.n + s.out_f64.n) * 8 + (s.i_a.n + s.i_b.n + s.i_c.n + s.i_d.n) * 4;
   return b;
@@ -411,7 +419,7 @@ iu_b200_grid* clone_to_device(iu_b200_grid* src, int device) {
     g->point_names = src->point_names; g->cell_names = src->cell_names; g->icell_names = src->icell_names;
     g->sort_mode = src->sort_mode; g->max_walk_steps = src->max_walk_steps; g->host_chunk = src->host_chunk;
     g->dev_batch = src->dev_batch; g->dynamic_tiles = src->dynamic_tiles; g->voxel_density = src->voxel_density;
-    g->time_kernels = src->time_kernels;
+    g->time_kernels = src->time_kernels; g->overlap_sort = src->overlap_sort; g->tiles_per_warp = src->tiles_per_warp;
     for (int k = 0; k < 3; ++k) { g->cmin[k] = src->cmin[k]; g->cmax[k] = src->cmax[k]; }
     g->vox_flagged = src->vox_flagged; g->vox_entries = src->vox_entries; g->vox_build_ms = 0;
     g->mesh_bytes = src->mesh_bytes; g->tree_depth = src->tree_depth;
@@ -517,6 +525,8 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     d_cells.release(); d_neigh.release(); d_centers.release();
     if (const char* env = std::getenv("IU_B200_NN_VOXEL_DENSITY")) g->voxel_density = std::max(0, std::atoi(env));
     if (const char* env = std::getenv("IU_B200_DYNAMIC_TILES")) g->dynamic_tiles = std::min(2, std::max(0, std::atoi(env)));   // A/B knob
+    if (const char* env = std::getenv("IU_B200_OVERLAP_SORT")) g->overlap_sort = std::atoi(env) != 0;                          // A/B knob
+    if (const char* env = std::getenv("IU_B200_TILES_PER_WARP")) g->tiles_per_warp = std::max(1, std::atoi(env));               // A/B knob
     if (const char* env = std::getenv("IU_B200_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(env));   // experiment knob
     build_voxel_table(g);
     // data tables
@@ -664,6 +674,13 @@ int iu_b200_grid_destroy(iu_b200_grid* g) {
     if (g->h_walk_sum) cudaFreeHost(g->h_walk_sum);
     if (g->walk_ev) cudaEventDestroy(g->walk_ev);
     if (g->ws_done) cudaEventDestroy(g->ws_done);
+    g->idx_alt2.release();
+    if (g->s_sort) cudaStreamDestroy(g->s_sort);
+    if (g->ev_enter) cudaEventDestroy(g->ev_enter);
+    for (int k = 0; k < 2; ++k) {
+      if (g->ev_sorted[k]) cudaEventDestroy(g->ev_sorted[k]);
+      if (g->ev_queried[k]) cudaEventDestroy(g->ev_queried[k]);
+    }
     if (g->s_in) cudaStreamDestroy(g->s_in);
     if (g->s_comp) cudaStreamDestroy(g->s_comp);
     if (g->s_out) cudaStreamDestroy(g->s_out);
@@ -918,6 +935,14 @@ static int set_option_one(iu_b200_grid* g, int option, int64_t value) {
       if (value < 0 || value > 2) break;
       g->dynamic_tiles = (int)value;
       return IU_B200_OK;
+    case IU_B200_OPT_OVERLAP_SORT:
+      if (value < 0 || value > 1) break;
+      g->overlap_sort = (int)value;
+      return IU_B200_OK;
+    case IU_B200_OPT_TILES_PER_WARP:
+      if (value < 1 || value > (1 << 20)) break;
+      g->tiles_per_warp = (int)value;
+      return IU_B200_OK;
     case IU_B200_OPT_TIME_KERNELS:
       if (value < 0 || value > 1) break;
       g->time_kernels = value != 0;
@@ -967,6 +992,7 @@ int iu_b200_get_stats(iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
     stats[IU_B200_STAT_DEVICES] = 1 + (int64_t)g->replicas.size();
     stats[IU_B200_STAT_REPLICATE_US] = (int64_t)(g->replicate_ms * 1e3);
     stats[IU_B200_STAT_BOUNDS_ERRORS] = (int64_t)bounds_errors();
+    stats[IU_B200_STAT_H2D_SKIPPED_BYTES] = (int64_t)g->h2d_skipped_bytes;
     // a multi-GPU handle reports the sums over its devices for the counters that add up
     for (iu_b200_grid* r : g->replicas) {
       int64_t rs[IU_B200_N_STATS];
@@ -974,7 +1000,7 @@ int iu_b200_get_stats(iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
       if (rc != IU_B200_OK) return rc;
       for (int k : {IU_B200_STAT_KERNEL_LAUNCHES, IU_B200_STAT_WALK_LIMIT_HITS, IU_B200_STAT_QUERIES, IU_B200_STAT_WORKSPACE_BYTES,
                     IU_B200_STAT_MESH_BYTES, IU_B200_STAT_NN_TREE_QUERIES, IU_B200_STAT_NOT_FOUND, IU_B200_STAT_QUERY_KERNEL_NS,
-                    IU_B200_STAT_QUERY_KERNEL_LAUNCHES, IU_B200_STAT_SORT_NS})
+                    IU_B200_STAT_QUERY_KERNEL_LAUNCHES, IU_B200_STAT_SORT_NS, IU_B200_STAT_H2D_SKIPPED_BYTES})
         stats[k] += rs[k];
       if (rs[IU_B200_STAT_BOUNDS_ERRORS] > 0) stats[IU_B200_STAT_BOUNDS_ERRORS] += rs[IU_B200_STAT_BOUNDS_ERRORS];
     }
@@ -998,6 +1024,7 @@ int iu_b200_reset_stats(iu_b200_grid* g) {
     for (int i = 0; i < CNT_N; ++i) g->seen[i] = c[i];
     g->n_launches = 0;
     g->n_queries = 0;
+    g->h2d_skipped_bytes = 0;
     collect_timings(g);
     g->timed_ns[0] = g->timed_ns[1] = 0;
     g->timed_launches[0] = g->timed_launches[1] = 0;
@@ -1022,11 +1049,78 @@ bool want_sort(const iu_b200_grid* g, int mode, int64_t m) {
 
 // Runs one logical batch as sub-batches of at most dev_batch queries; each sub-batch is optionally
 // Morton-sorted (key, index) and processed through the permutation.
+// Sub-batch view of a logical batch
+QueryArgs sub_batch(const QueryArgs& a, int64_t off, int64_t m, size_t out_row) {
+  QueryArgs b = a;
+  b.n = m;
+  b.r = a.r + 3 * off;
+  b.i_cell = a.i_cell ? a.i_cell + off : nullptr;
+  b.out_f64 = a.out_f64 ? a.out_f64 + out_row * off : nullptr;
+  b.out_i32 = a.out_i32 ? a.out_i32 + off : nullptr;
+  b.out2_f64 = a.out2_f64 ? a.out2_f64 + off : nullptr;
+  b.perm = nullptr;
+  return b;
+}
+
+// Several sorted sub-batches: the curve keys + radix sort of sub-batch k+1 run on a second, high-priority stream while
+// k_query works on sub-batch k.  The sort is HBM-bound, k_query is L1/latency-bound, so they share the SMs well - but
+// only if k_query leaves room: its warps retire after tiles_per_warp tiles (short-lived CTAs instead of a persistent
+// grid), and the block scheduler fills freed slots with the sort's CTAs first.  Two permutation buffers alternate.
+void run_query_overlapped(iu_b200_grid* g, const QueryArgs& a, cudaStream_t s, size_t out_row) {
+  const int64_t n = a.n, step = g->dev_batch;
+  const int end_bit = morton_end_bit(g->dg);
+  g->keys.ensure(step); g->keys_alt.ensure(step); g->idx.ensure(step); g->idx_alt.ensure(step); g->idx_alt2.ensure(step);
+  g->sort_temp.ensure(sort_temp_bytes(step, end_bit));
+  if (!g->s_sort) {
+    int lo = 0, hi = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CU(cudaStreamCreateWithPriority(&g->s_sort, cudaStreamNonBlocking, hi));
+    CU(cudaEventCreateWithFlags(&g->ev_enter, cudaEventDisableTiming));
+    for (int k = 0; k < 2; ++k) {
+      CU(cudaEventCreateWithFlags(&g->ev_sorted[k], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&g->ev_queried[k], cudaEventDisableTiming));
+    }
+  }
+  uint32_t* perm[2] = {g->idx_alt.p, g->idx_alt2.p};
+  CU(cudaEventRecord(g->ev_enter, s));                       // the caller's inputs are ready from here on
+  CU(cudaStreamWaitEvent(g->s_sort, g->ev_enter, 0));
+  const int64_t n_sub = (n + step - 1) / step;
+  auto enqueue_sort = [&](int64_t k) {
+    const int64_t off = k * step, m = std::min(step, n - off);
+    if (k >= 2) CU(cudaStreamWaitEvent(g->s_sort, g->ev_queried[k & 1], 0));   // the query that read this buffer last
+    TimedScope ts(g, g->s_sort, 1);
+    g->n_launches += launch_morton_sort(g->dg, m, a.r + 3 * off, a.mode == QM_NEAREST || !a.i_cell ? nullptr : a.i_cell + off, g->keys.p,
+                                        g->keys_alt.p, g->idx.p, perm[k & 1], g->sort_temp.p, g->sort_temp.n, nullptr, g->s_sort);
+    ts.stop();
+    CU(cudaEventRecord(g->ev_sorted[k & 1], g->s_sort));
+  };
+  enqueue_sort(0);
+  for (int64_t k = 0; k < n_sub; ++k) {
+    const int64_t off = k * step, m = std::min(step, n - off);
+    if (k + 1 < n_sub) enqueue_sort(k + 1);
+    QueryArgs b = sub_batch(a, off, m, out_row);
+    b.perm = perm[k & 1];
+    b.dynamic = g->dynamic_tiles;
+    b.tiles_per_warp = k + 1 < n_sub ? g->tiles_per_warp : 0;   // nothing runs beside the last one
+    CU(cudaStreamWaitEvent(s, g->ev_sorted[k & 1], 0));
+    TimedScope tq(g, s, 0);
+    g->n_launches += launch_query(g->dg, b, s);
+    tq.stop();
+    CU(cudaEventRecord(g->ev_queried[k & 1], s));
+    CU(cudaGetLastError());
+  }
+  g->n_queries += n;
+}
+
 void run_query(iu_b200_grid* g, QueryArgs a, cudaStream_t s) {
   WorkspaceScope ws(g, s);
   const int64_t n = a.n;
   const int64_t step = g->dev_batch;
   const size_t out_row = a.mode == QM_INTERP || a.mode == QM_INTERP_ICELL || a.mode == QM_INTERP_CELL ? (size_t)a.n_vars : 1;
+  if (g->overlap_sort && g->dynamic_tiles == 1 && g->sort_mode != 3 && n > step && want_sort(g, a.mode, std::min(step, n - (n - 1) / step * step))) {
+    run_query_overlapped(g, a, s, out_row);
+    return;
+  }
   for (int64_t off = 0; off < n; off += step) {
     const int64_t m = std::min(step, n - off);
     QueryArgs b = a;
@@ -1580,7 +1674,14 @@ int query_host_one(iu_b200_grid* g, int mode, int64_t n, const double* r, int n_
     }
     auto h2d = [&](Slot& sl, int64_t off, int64_t m) {
       CU(cudaMemcpyAsync(sl.r.p, r + 3 * off, (size_t)m * 24, cudaMemcpyHostToDevice, g->s_in));
-      if (mode != QM_NEAREST) CU(cudaMemcpyAsync(sl.i_a.p, i_cell + off, (size_t)m * 4, cudaMemcpyHostToDevice, g->s_in));
+      if (mode == QM_NEAREST) return;
+      // a chunk without a single hint (benchmark.f90's first pass: i_cell(:) = 0) does not send its i_cell over the bus:
+      // the host scans the 4 bytes per query (while the previous chunks are in flight) and the device buffer is zeroed
+      const int32_t* h = i_cell + off;
+      int any_hint = 0;
+      for (int64_t i = 0; i < m; ++i) any_hint |= h[i] > 0;
+      if (any_hint) CU(cudaMemcpyAsync(sl.i_a.p, h, (size_t)m * 4, cudaMemcpyHostToDevice, g->s_in));
+      else { CU(cudaMemsetAsync(sl.i_a.p, 0, (size_t)m * 4, g->s_in)); g->h2d_skipped_bytes += (size_t)m * 4; }
     };
     auto compute = [&](Slot& sl, int64_t m) {
       run_query(g, make_args(g, mode, m, sl.r.p, n_vars, i_vars, i_var, sl.i_a.p, sl.out_f64.p, sl.i_b.p, fused ? sl.r1.p : nullptr), g->s_comp);

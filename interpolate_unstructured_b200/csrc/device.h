@@ -98,6 +98,7 @@ struct QueryArgs {
   int ivars[MAX_VARS] = {0};        // 0-based columns
   int max_steps = 1 << 20;
   int dynamic = 0;                  // 1: draw tiles of consecutive queries from a ticket counter (sorted batches only)
+  int tiles_per_warp = 0;           // dynamic = 1: warps retire after this many tiles (0 = persistent CTAs)
 };
 
 struct WalkArgs {

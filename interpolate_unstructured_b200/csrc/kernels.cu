@@ -1009,6 +1009,7 @@ struct QueryKernelParams {
   int pairs;                      // 1 / 2: the requested variables come in adjacent, aligned groups of 2 / 4 columns
   unsigned long long* ticket;     // work counter of the dynamically scheduled variants (zeroed before the launch)
   int sched;
+  int tiles_per_warp;             // SCHED = 1: a warp retires after this many tiles (0: never = persistent CTAs)
   int ivars[MAX_VARS];
 };
 
@@ -1199,9 +1200,14 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
   int64_t t = SCHED ? 0 : (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t tile = 0;
   int sub = STILE / 32;
+  int drawn = 0;
   for (;; t += (int64_t)gridDim.x * blockDim.x) {
     if (SCHED) {
       if (sub == STILE / 32) {
+        // a bounded number of tiles per warp turns the persistent grid into many short-lived CTAs: the slots they
+        // free let the kernels of another stream (the sort of the next sub-batch, api.cu: run_query) run beside this one
+        if (P.tiles_per_warp && drawn == P.tiles_per_warp) break;
+        ++drawn;
         unsigned long long b = 0;
         if (lane == 0) b = atomicAdd(P.ticket, (unsigned long long)STILE);
         tile = (int64_t)__shfl_sync(0xffffffffu, b, 0);
@@ -1589,6 +1595,11 @@ void launch_query_static(const QueryKernelParams& P, int depth, cudaStream_t s) 
   }
   int64_t need = (P.n + QUERY_THREADS - 1) / QUERY_THREADS;
   int g = (int)(need < blocks ? need : blocks);
+  if (SCHED && P.tiles_per_warp > 0) {   // every tile must find a warp: tiles / (warps per CTA x tiles per warp) CTAs
+    const int64_t tiles = (P.n + IU_STILE - 1) / IU_STILE;
+    const int64_t per_cta = (int64_t)(QUERY_THREADS / 32) * P.tiles_per_warp;
+    g = (int)std::max<int64_t>(1, (tiles + per_cta - 1) / per_cta);
+  }
   if (SCHED) cudaMemsetAsync(P.ticket, 0, sizeof(unsigned long long), s);
   k_query<CT, MODE, NV, SCHED><<<g, QUERY_THREADS, dyn, s>>>(P);
 }
@@ -1838,6 +1849,7 @@ int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
   }
   P.ticket = a.dynamic ? g.counters + CNT_TICKET : nullptr;
   P.sched = a.dynamic;
+  P.tiles_per_warp = a.tiles_per_warp;
   if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, g.depth, s);
   else if (g.cell_type == IU_QUAD_CT) launch_query_ct<IU_QUAD_CT>(a.mode, P, g.depth, s);
   else launch_query_ct<IU_TETRA_CT>(a.mode, P, g.depth, s);

@@ -315,3 +315,53 @@ def test_plain_c_driver_runs_the_reference_test_programs():
     out = subprocess.run([exe, os.path.join(root, "tests", "golden")], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout + out.stderr
     assert out.stdout.count("PASSED") == 5
+
+
+@pytest.mark.parametrize("kind,n", [("tetra", 16), ("quad", 120)])
+def test_sort_of_next_sub_batch_overlaps_the_query_kernel(kind, n):
+    """run_query_overlapped: several sorted sub-batches per call, the sort of sub-batch k+1 on a second stream beside
+    k_query of sub-batch k (short-lived CTAs, two permutation buffers).  Small IU_B200_OPT_DEV_BATCH values force many
+    sub-batches; results must equal the oracle's and the non-overlapped path's for cold, hinted and fused calls."""
+    import torch
+    pts, cells = {"tetra": meshgen.kuhn_tet_mesh, "quad": meshgen.quad_mesh}[kind](n, seed=5)
+    nb = api.build_cell_neighbors(cells, pts, kind)
+    pd = meshgen.smooth_fields(pts, 4)
+    cd = np.arange(1, len(cells) + 1, dtype=np.float64)
+    g = api.Grid.from_arrays(kind, pts, cells, nb, pd, cell_data=cd)
+    o = OracleGrid.from_arrays(kind, pts, cells, nb, pd, cell_data=cd)
+    lo, hi = pts.min(0), pts.max(0)
+    nq = 300_001
+    r = meshgen.uniform_queries(nq, lo - 0.02 * (hi - lo), hi + 0.02 * (hi - lo), seed=61)
+    ores, oic = o.interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -6.5), nn="brute", nthreads=NT)
+    hint = np.where((np.arange(nq) % 3 == 0) & (oic >= 1), oic, 0).astype(np.int32)
+    ohres, ohic = o.interpolate_at(r, [1, 2, 3, 4], var_at_r=np.full((nq, 4), -6.5), i_cell=hint.copy(), nn="brute", nthreads=NT)
+    dev = torch.device("cuda", 0)
+    r_t = torch.from_numpy(r).to(dev)
+    g.set_option(api.OPT_SORT_QUERIES, 1)
+    for batch, tpw, overlap in ((40_000, 1, 1), (37_123, 8, 1), (150_000, 3, 1), (40_000, 8, 0)):
+        g.set_option(api.OPT_DEV_BATCH, batch)
+        g.set_option(api.OPT_TILES_PER_WARP, tpw)
+        g.set_option(api.OPT_OVERLAP_SORT, overlap)
+        for rep in range(2):                               # the second call reuses buffers, stream and events
+            ic_t = torch.zeros(nq, dtype=torch.int32, device=dev)
+            out_t = torch.full((nq, 4), -6.5, dtype=torch.float64, device=dev)
+            g.iu_interpolate_at_dev(r_t, [1, 2, 3, 4], out_t, ic_t)
+            g.check_dev()
+            assert np.array_equal(ic_t.cpu().numpy(), oic) and np.array_equal(out_t.cpu().numpy(), ores), (batch, tpw, overlap)
+        ic_t = torch.from_numpy(hint.copy()).to(dev)
+        out_t = torch.full((nq, 4), -6.5, dtype=torch.float64, device=dev)
+        g.iu_interpolate_at_dev(r_t, [1, 2, 3, 4], out_t, ic_t)
+        g.check_dev()
+        assert np.array_equal(ic_t.cpu().numpy(), ohic) and np.array_equal(out_t.cpu().numpy(), ohres), (batch, tpw, overlap)
+        # fused call and nearest centre through the same path
+        ic_t = torch.zeros(nq, dtype=torch.int32, device=dev)
+        cr_t = torch.full((nq,), -2.5, dtype=torch.float64, device=dev)
+        g.iu_interpolate_and_cell_scalar_at_dev(r_t, [1, 2, 3, 4], 1, out_t, cr_t, ic_t)
+        idx_t = torch.zeros(nq, dtype=torch.int32, device=dev)
+        g.find_nearby_cell_kdtree_dev(r_t, idx_t)
+        g.check_dev()
+        assert np.array_equal(ic_t.cpu().numpy(), oic)
+        assert np.array_equal(cr_t.cpu().numpy()[oic >= 1], oic[oic >= 1].astype(np.float64))
+        assert np.array_equal(idx_t.cpu().numpy(), o.nearest(r, "brute", nthreads=NT)[0])
+    st = g.stats()
+    assert st["walk_limit_hits"] == 0
