@@ -151,9 +151,17 @@ __device__ __forceinline__ V3 ld3(const double* p) { return {__ldg(p), __ldg(p +
 // 32-byte load (sm_100a: LDG.E.256): one L1 tag lookup per lane for a whole leaf slot / a third of
 // a record's normals instead of two.  p must be 32-byte aligned.
 struct D4 { double x, y, z, w; };
+#ifndef IU_LD256_SPLIT
+#define IU_LD256_SPLIT 0   // 1: every 32-byte gather as two 16-byte loads (A/B of the LSU data-pipe cost of LDG.256)
+#endif
 __device__ __forceinline__ D4 ld256(const double* p) {
   D4 r;
+#if IU_LD256_SPLIT
+  asm volatile("ld.global.nc" IU_LTC_M ".v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+  asm volatile("ld.global.nc" IU_LTC_M ".v2.f64 {%0,%1}, [%2];" : "=d"(r.z), "=d"(r.w) : "l"(p + 2));
+#else
   asm volatile("ld.global.nc" IU_LTC_M ".v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(r.x), "=d"(r.y), "=d"(r.z), "=d"(r.w) : "l"(p));
+#endif
   return r;
 }
 __device__ __forceinline__ uint4 ld128u(const uint4* p) {
@@ -1432,8 +1440,11 @@ __global__ void k_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const 
   r[3 * i + 2] = ndim > 2 ? Y[2] : 0.0;     // "Set unused coordinates to zero", :1045-1047
 }
 
+#ifndef IU_TRACE_MIN_BLOCKS
+#define IU_TRACE_MIN_BLOCKS 4   // resident CTAs per SM k_trace is compiled for (128 registers; 1 / 4 / 6 / 8 measured: 36.7 / 31.6 / 35.6 / 35.2 ms per 500k lines)
+#endif
 template <int CT>
-__global__ void __launch_bounds__(128) k_trace(const double* __restrict__ rec, const int32_t* __restrict__ dev_of_orig,
+__global__ void __launch_bounds__(128, IU_TRACE_MIN_BLOCKS) k_trace(const double* __restrict__ rec, const int32_t* __restrict__ dev_of_orig,
                                                const double* __restrict__ pd, int pd_stride, const int32_t* __restrict__ icd,
                                                int n_cells, unsigned long long* counters, const TraceArgs a) {
   constexpr int PPC = CT == IU_TRIANGLE_CT ? 3 : 4;

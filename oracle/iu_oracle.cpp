@@ -545,11 +545,24 @@ void sub_int_builtin(int integrand, int ndim, int nvar, const double* field, dou
   for (int i = 0; i < nvar; ++i) dy_var[i] = v;
 }
 
+// smallest |err - 1| over all accept / reject decisions (:1165) of the latest batch: how far the closest decision was from
+// flipping.  The CUDA tracer's curves agree to 1e-10 (pow() differs in the last bit), so a margin far above that means
+// no decision of the batch can have gone the other way on the device.
+double g_trace_margin = 1e300;
+
 void integrate_along_field(const Grid& g, int ndim, int nvar, int integrand, const int* i_field, double min_dx,
                            double max_dx, int max_steps, double rtol, double atol, bool reverse, double* y,
                            double* y_field, int& n_steps, bool axisymmetric, int i_icell_mask, int mask_value,
                            int* boundary_material, int nn_mode) {
   const double safety_fac = 0.8, inv_24 = 1 / 24.0, inv_9 = 1 / 9.0, min_radius = 1e-12, eps = 1e-8;
+  double line_margin = 1e300;
+  struct MarginGuard {
+    double& m;
+    ~MarginGuard() {
+#pragma omp critical(iu_trace_margin)
+      if (m < g_trace_margin) g_trace_margin = m;
+    }
+  } margin_guard{line_margin};
   const int nt = ndim + nvar;
   constexpr int MAXT = 8;
   double ys[MAXT], y_2nd[MAXT], k[4][MAXT], field[3], scales[MAXT];
@@ -616,6 +629,7 @@ void integrate_along_field(const Grid& g, int ndim, int nvar, int integrand, con
       sum += e * e;
     }
     const double err = std::sqrt(sum / 3);
+    if (!(dx < 2 * min_dx) && std::fabs(err - 1) < line_margin) line_margin = std::fabs(err - 1);
     if (err <= 1 || dx < 2 * min_dx) {                                                                    // :1165-1176
       n_steps = n_steps + 1;
       if (n_steps > max_steps) return;
@@ -904,6 +918,7 @@ void iu_oracle_integrate_along_field(void* h, int64_t n, int ndim, int nvar, int
   const Grid& g = *(Grid*)h;
   const size_t ny = (size_t)(ndim + nvar) * max_steps, nf = (size_t)ndim * max_steps;
   int nt = eff_threads(nthreads); (void)nt;
+  g_trace_margin = 1e300;
 #pragma omp parallel for num_threads(nt) schedule(dynamic, 64)
   for (int64_t i = 0; i < n; ++i)
     integrate_along_field(g, ndim, nvar, integrand, i_field, min_dx, max_dx, max_steps, rtol, atol, reverse != 0, y + ny * i,
@@ -963,6 +978,9 @@ int iu_oracle_cell_neighbors(int n_points, int n_cells, int ppc, int n_points_fa
   }
   return 0;
 }
+
+// smallest |err - 1| over the accept / reject decisions of the latest iu_oracle_integrate_along_field batch
+double iu_oracle_last_trace_margin() { return g_trace_margin; }
 
 int iu_oracle_max_threads() {
 #ifdef _OPENMP

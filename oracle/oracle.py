@@ -58,6 +58,7 @@ def lib():
                                                       C.c_int, c_ip, C.c_int, C.c_int]
         L.iu_oracle_cell_neighbors.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, c_dp, c_ip, c_ip]
         L.iu_oracle_max_threads.restype = C.c_int
+        L.iu_oracle_last_trace_margin.restype = C.c_double
         L.iu_oracle_benchmark_pass.restype = C.c_double
         L.iu_oracle_benchmark_pass.argtypes = [C.c_void_p, C.c_int64, c_dp, C.c_int, c_ip, c_dp, c_ip, C.c_int]
         _lib = L
@@ -282,6 +283,7 @@ class OracleGrid:
                                               int(max_steps), float(rtol), float(atol), int(bool(reverse)), _d(y), _d(yf), _i(ns),
                                               int(bool(axisymmetric)), int(i_icell_mask), int(mask_value), _i(bm),
                                               0 if nn == "kdtree2" else 1, nthreads)
+        self.last_trace_margin = float(lib().iu_oracle_last_trace_margin())   # min |err - 1| over the accept / reject decisions
         return y, yf, ns, bm
 
     def point_is_inside_cell(self, r, i_cell):

@@ -79,6 +79,11 @@ def test_trace_parity(kind, n, ndim, variant):
     gy, gf, gns, gbm = g.iu_integrate_along_field(y, i_field, 1e-4, 2e-2, 1e-4, 1e-6, **kw)
     oy, of, ons, obm = o.integrate_along_field(y0, i_field, 1e-4, 2e-2, max_steps, 1e-4, 1e-6, **kw)
     _compare(gy, gf, gns, gbm, oy, of, ons, obm, max_steps)
+    # margin report: the closest any accept / reject decision (err <= 1, :1165) of this batch came to flipping.  The curves
+    # agree to 1e-10 and err is a ratio of O(1) quantities, so a margin orders of magnitude above that rules out a
+    # decision that went the other way on the device (n_steps equality above is then not a coincidence).
+    assert o.last_trace_margin > 1e-7, f"an accept/reject decision came within {o.last_trace_margin:.1e} of flipping"
+    print(f"trace {kind} {variant}: closest |err - 1| over all decisions = {o.last_trace_margin:.2e}")
     # lines traced in Morton order of their seeds (forced on for this small batch) give the same bits as in input order
     g.set_option(api.OPT_SORT_QUERIES, 1)
     y2 = np.full((nl, max_steps, ndim + nvar), np.nan)

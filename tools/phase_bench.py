@@ -98,8 +98,18 @@ def main():
     def icell_ps():
         g.iu_interpolate_at_icell_dev(rs, I_VARS, out, hs)
 
+    # upper bound of what grouping the queries of a warp by CELL could give: queries physically ordered by the cell that
+    # contains them (original cell id: cube-major for the Kuhn mesh), processed without a permutation
+    order_c = torch.argsort(hint.long() * 64 + torch.randint(0, 64, (nq,), device=dev))
+    rc = r[order_c].contiguous()
+    del order_c
+
+    def interp_bycell():
+        ic.zero_()
+        g.iu_interpolate_at_dev(rc, I_VARS, out, ic)
+
     res = {}
-    for name, fn in [("nearest_presorted", presorted(nearest_ps)), ("interp_presorted", presorted(interp_ps)),
+    for name, fn in [("interp_grouped_by_cell", presorted(interp_bycell)), ("nearest_presorted", presorted(nearest_ps)), ("interp_presorted", presorted(interp_ps)),
                      ("warm_presorted", presorted(warm_ps)), ("icell_presorted", presorted(icell_ps)),("nearest", nearest), ("cell", cell), ("interp", interp), ("warm", warm), ("icell", icell)]:
         fn()
         g.check_dev()
