@@ -841,7 +841,7 @@ __device__ __forceinline__ int nn_voxel(const VoxelGrid& V, const double* __rest
     if (IU_OOB((long long)e.x >= g_lim[0] || (long long)e.y >= g_lim[0] || (long long)e.z >= g_lim[0] || (long long)e.w >= g_lim[0])) break;
     D4 c[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) c[j] = ld256(cen32 + 4 * (size_t)sl[j]);
+    for (int j = 0; j < 4; ++j) c[j] = ld256(cen32 + 4 * (size_t)sl[j]);   // (predicating off the padded repeats: fewer wavefronts, +7 % instructions, slower)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const double dx = c[j].x - qx, dy = c[j].y - qy, dz = c[j].z - qz;
@@ -1408,9 +1408,14 @@ __global__ void __launch_bounds__(QUERY_THREADS) k_walk(const double* __restrict
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < a.n; t += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = a.perm ? (int64_t)LD_STREAM(a.perm + t) : t;
     if (IU_OOB(i < 0 || i >= a.n)) continue;
-    const int h = a.ic0[i];
+    // through a permutation the ray's inputs are scattered reads: streaming loads with 64-byte DRAM fetches, like k_query's
+    const int h = a.perm ? LD_STREAM(a.ic0 + i) : a.ic0[i];
     if (h < 1 || h > n_cells) { atomicAdd(counters + CNT_HINT_ERROR, 1ULL); continue; }
-    const V3 r0 = ld3(a.r0 + 3 * i), r1 = ld3(a.r1 + 3 * i);
+    V3 r0, r1;
+    if (a.perm) {
+      r0 = V3{LD_STREAM(a.r0 + 3 * i), LD_STREAM(a.r0 + 3 * i + 1), LD_STREAM(a.r0 + 3 * i + 2)};
+      r1 = V3{LD_STREAM(a.r1 + 3 * i), LD_STREAM(a.r1 + 3 * i + 1), LD_STREAM(a.r1 + 3 * i + 2)};
+    } else { r0 = ld3(a.r0 + 3 * i); r1 = ld3(a.r1 + 3 * i); }
     int ic1, n_steps = 0, status; V3 r_p; bool early;
     walk_ray<PPC>(rec, r0, r1, __ldg(dev_of_orig + h), a.max_steps, mask, ic1, r_p, n_steps, status, early);
     a.ic1[i] = ic1 >= 1 ? __ldg(orig_of_dev + (ic1 - 1)) : ic1;

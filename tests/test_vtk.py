@@ -72,3 +72,33 @@ def test_grid_write_vtk_from_device(tmp_path, name, ct):
     cd = {g.cell_data_name(i): g.get_cell_data(i)[:, 0] for i in range(1, g.n_cell_data + 1)} if g.n_cell_data else {}
     icd = {g.icell_data_name(i): g.get_icell_data(i)[:, 0] for i in range(1, g.n_icell_data + 1)} if g.n_icell_data else {}
     assert open(path, "rb").read() == vtk_oracle.vtu_bytes(ct, pts, cells1, cd, icd, pd)
+
+
+@pytest.mark.gpu
+def test_grid_write_vtk_keeps_points_no_cell_references(tmp_path):
+    """meshes converted by meshio often carry points that no cell uses (and duplicates of merged points).
+    iu_write_vtk writes ug%points unchanged (m_interp_unstructured.f90:961), so those points must come back with their
+    coordinates, not as zeros; named columns given to from_arrays must be the VTU array names."""
+    pts, cells = meshgen.kuhn_tet_mesh(3, jitter=0.1, seed=3)
+    orphans = np.array([[7.5, -2.25, 3.125], [pts[5, 0], pts[5, 1], pts[5, 2]], [-1.0, -1.0, -1.0]])
+    pts2 = np.concatenate([pts[:10], orphans[:2], pts[10:], orphans[2:]])          # orphans in the middle and at the end
+    remap = np.concatenate([np.arange(10), np.arange(10, len(pts)) + 2])
+    cells2 = remap[cells].astype(np.int32)
+    nb = api.build_cell_neighbors(cells2, pts2, "tetra")
+    rng = np.random.default_rng(3)
+    pd = rng.normal(size=(len(pts2), 2))
+    cd = rng.normal(size=(len(cells2), 1))
+    g = api.Grid.from_arrays("tetra", pts2, cells2, nb, pd, cell_data=cd, point_names=["phi", "rho"], cell_names=["vol"])
+    assert g.iu_get_point_data_index("rho") == 2 and g.iu_get_cell_data_index("vol") == 1 and g.iu_get_point_data_index("nope") == -1
+    p_back, c_back = g.export_mesh()
+    assert np.array_equal(p_back, pts2) and np.array_equal(c_back, cells2 + 1)
+    path = str(tmp_path / "orphans.vtu")
+    g.iu_write_vtk(path)
+    got = open(path, "rb").read()
+    assert got == vtk_oracle.vtu_bytes(3, pts2, cells2 + 1, {"vol": cd[:, 0]}, {}, {"phi": pd[:, 0], "rho": pd[:, 1]})
+    arrays = vtk_oracle.parse_vtu(got)
+    assert np.array_equal(arrays["Points"].reshape(-1, 3)[[10, 11, len(pts2) - 1]], orphans.astype(np.float32))
+    # queries still resolve (the orphans belong to no cell and change nothing)
+    r = meshgen.uniform_queries(2000, [0.1] * 3, [0.9] * 3, seed=2)
+    _, ic = g.iu_interpolate_at(r, [1])
+    assert (ic >= 1).all()
