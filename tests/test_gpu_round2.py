@@ -365,3 +365,53 @@ def test_sort_of_next_sub_batch_overlaps_the_query_kernel(kind, n):
         assert np.array_equal(idx_t.cpu().numpy(), o.nearest(r, "brute", nthreads=NT)[0])
     st = g.stats()
     assert st["walk_limit_hits"] == 0
+
+
+@pytest.mark.parametrize("kind,n,jitter", [("tetra", 8, 0.0), ("tetra", 8, 0.1), ("quad", 24, 0.0), ("quad", 24, 0.2), ("triangle", 24, 0.0)])
+def test_queries_on_vertices_edges_faces_and_centres(kind, n, jitter):
+    """north_star: 'query points lying exactly on shared faces are ... resolved by the reference's own comparison order'.
+    Queries AT mesh vertices, edge midpoints, face centroids and cell centres (zero-length rays, :689-692) of lattice and
+    jittered meshes: every face-distance tie (strict '<', first face wins, :755), every `distance_left > 0` decision on
+    a face (:704) and every nearest-centre tie (lowest cell index, as the oracle's exact search) must come out as in
+    the oracle, bit for bit, cold and with hints; walks with explicit start positions too."""
+    gen = {"tetra": meshgen.kuhn_tet_mesh, "quad": meshgen.quad_mesh, "triangle": meshgen.triangle_mesh}[kind]
+    pts, cells = gen(n, jitter=jitter, seed=4)
+    nb = api.build_cell_neighbors(cells, pts, kind)
+    pd = meshgen.smooth_fields(pts, 3)
+    g = api.Grid.from_arrays(kind, pts, cells, nb, pd)
+    o = OracleGrid.from_arrays(kind, pts, cells, nb, pd)
+    P = pts[cells]                                                   # (Nc, ppc, 3)
+    ppc = cells.shape[1]
+    q = [pts, P.mean(1)]                                             # vertices, (approximate) cell centres
+    q.append(o.cell_centers)                                         # the exact centres: zero-length rays
+    for a in range(ppc):
+        for b in range(a + 1, ppc):
+            q.append(0.5 * (P[:, a] + P[:, b]))                      # edge midpoints
+            q.append(P[:, a] + 0.25 * (P[:, b] - P[:, a]))
+    if ppc == 4 and kind == "tetra":
+        for a in range(4):
+            q.append(P[:, [k for k in range(4) if k != a]].mean(1))  # face centroids
+    r = np.ascontiguousarray(np.concatenate(q))
+    nq = len(r)
+    for sort in (0, 1):
+        g.set_option(api.OPT_SORT_QUERIES, sort)
+        oidx = o.nearest(r, "brute", nthreads=NT)[0]
+        assert (g.find_nearby_cell_kdtree(r) == oidx).all(), sort
+        ores, oic = o.interpolate_at(r, [1, 2, 3], var_at_r=np.full((nq, 3), -8.5), nn="brute", nthreads=NT)
+        res, ic = g.iu_interpolate_at(r, [1, 2, 3], var_at_r=np.full((nq, 3), -8.5))
+        assert (ic == oic).all(), (sort, int((ic != oic).sum()))
+        assert np.array_equal(res, ores), sort
+        # hints: the cell found, and a neighbour of it (the walk then crosses exactly the face / vertex the query sits on)
+        nbr = np.where(oic >= 1, nb[np.maximum(oic, 1) - 1, 0] + 1, 0)
+        for hint in (np.maximum(oic, 0).astype(np.int32), np.where(nbr >= 1, nbr, np.maximum(oic, 0)).astype(np.int32)):
+            ohres, ohic = o.interpolate_at(r, [1, 2, 3], var_at_r=np.full((nq, 3), -8.5), i_cell=hint.copy(), nn="brute", nthreads=NT)
+            hres, hic = g.iu_interpolate_at(r, [1, 2, 3], var_at_r=np.full((nq, 3), -8.5), i_cell=hint.copy())
+            assert (hic == ohic).all() and np.array_equal(hres, ohres), sort
+    # explicit rays between special points: from every cell's first vertex to its last vertex's neighbour cell centre
+    r0 = np.ascontiguousarray(P[:, 0])
+    r1 = np.ascontiguousarray(o.cell_centers[np.maximum(nb[:, -1], 0)])
+    ic0 = np.arange(1, len(cells) + 1, dtype=np.int32)
+    want = o.get_cell_through_neighbors(10 ** 6, r0, r1, ic0)
+    got = g.iu_get_cell_through_neighbors(10 ** 6, r0, r1, ic0)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b, equal_nan=True)
