@@ -96,6 +96,7 @@ extern "C" {
                                         * derive from mesh / query data and count the violations here */
 #define IU_B200_STAT_H2D_SKIPPED_BYTES 18 /* host API: bytes of i_cell NOT uploaded because a whole pipeline chunk carried no
                                            * hint (the device buffer is zeroed instead) */
+#define IU_B200_STAT_TREE_BUILD_US 19    /* wall time of the kd-tree build at grid creation (device build; IU_B200_HOST_TREE=1: host) */
 #define IU_B200_N_STATS 20
 
 typedef struct iu_b200_grid iu_b200_grid; /* opaque; replaces type(iu_grid_t), :24-59 */

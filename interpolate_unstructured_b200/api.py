@@ -33,7 +33,7 @@ OPT_SORT_QUERIES, OPT_MAX_WALK_STEPS, OPT_HOST_CHUNK, OPT_DEV_BATCH, OPT_TIME_KE
 OPT_NN_VOXEL_DENSITY, OPT_OVERLAP_SORT, OPT_TILES_PER_WARP = 7, 8, 9
 STAT_NAMES = ["kernel_launches", "walk_limit_hits", "queries", "workspace_bytes", "mesh_bytes", "tree_depth",
               "not_found", "query_kernel_ns", "query_kernel_launches", "sort_ns", "nn_voxels", "nn_voxels_tree", "nn_voxel_entries",
-              "nn_tree_queries", "nn_voxel_build_us", "devices", "replicate_us", "bounds_errors", "h2d_skipped_bytes", "reserved19"]
+              "nn_tree_queries", "nn_voxel_build_us", "devices", "replicate_us", "bounds_errors", "h2d_skipped_bytes", "tree_build_us"]
 
 c_dp = C.POINTER(C.c_double)
 c_ip = C.POINTER(C.c_int32)

@@ -142,7 +142,7 @@ struct iu_b200_grid {
   // Further replicas of the mesh on other GPUs (iu_b200_grid_replicate): full single-device grids of their own.  The
   // host-buffer batch calls split [0, n) into one contiguous slab per device and run them concurrently.
   std::vector<iu_b200_grid*> replicas;
-  double replicate_ms = 0;
+  double replicate_ms = 0, tree_build_ms = 0;
 };
 
 namespace {
@@ -494,14 +494,15 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
         g->cmin[k] = v < g->cmin[k] ? v : g->cmin[k];
         g->cmax[k] = v > g->cmax[k] ? v : g->cmax[k];
       }
-    KdTreeHost tree;
-    build_kdtree(h_centers.data(), n_cells, tree);
     std::vector<double>().swap(h_centers);
-    d.n_leaves = tree.n_leaves;
-    d.n_internal = tree.n_leaves - 1;
-    for (int l = 1; l < tree.n_leaves; l <<= 1) ++g->tree_depth;
+    // the nearest-centre kd-tree (build_kdtree, :251-262): built on the device from the device copy of the centres
+    // (tree_build.cu); IU_B200_HOST_TREE=1 selects the host builder of host_mesh.cpp (same kind of tree) for A/B
+    d.n_leaves = (n_cells + LEAF - 1) / LEAF;
+    d.n_internal = d.n_leaves - 1;
+    for (int l = 1; l < d.n_leaves; l <<= 1) ++g->tree_depth;
     d.depth = g->tree_depth;
-    const size_t n_slots = (size_t)tree.n_leaves * LEAF;
+    const size_t n_slots = (size_t)d.n_leaves * LEAF;
+    const size_t box_floats = 8 * (size_t)(2 * d.n_leaves - 1);
     CU(cudaMalloc((void**)&d.orig_of_dev, n_slots * 4));
     CU(cudaMalloc((void**)&d.dev_of_orig, ((size_t)n_cells + 1) * 4));
     CU(cudaMalloc((void**)&d.centers4, n_slots * 24));
@@ -510,24 +511,40 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
     CU(cudaMalloc((void**)&d.counters, CNT_N * sizeof(unsigned long long)));
     CU(cudaMemsetAsync(d.counters, 0, CNT_N * sizeof(unsigned long long), s));
     CU(cudaMemsetAsync(d.dev_of_orig, 0, ((size_t)n_cells + 1) * 4, s));
-    if (d.n_internal > 0) {
-      // nodes with their children's splits alongside: {split, split(2i+1), split(2i+2), dimensions}
-      std::vector<double> fat((size_t)4 * d.n_internal, 0.0);
-      for (int i = 0; i < d.n_internal; ++i) {
-        unsigned long long dims = tree.sdim[i];
-        fat[4 * (size_t)i] = tree.split[i];
-        for (int c = 0; c < 2; ++c) {
-          const long long ch = 2LL * i + 1 + c;
-          if (ch < d.n_internal) { fat[4 * (size_t)i + 1 + c] = tree.split[ch]; dims |= (unsigned long long)tree.sdim[ch] << (2 + 2 * c); }
+    if (d.n_internal > 0) CU(cudaMalloc((void**)&d.fat, (size_t)d.n_internal * 32));
+    CU(cudaMalloc((void**)&d.box, std::max<size_t>(32, box_floats * sizeof(float))));
+    const auto t_tree = std::chrono::steady_clock::now();
+    if (std::getenv("IU_B200_HOST_TREE")) {
+      std::vector<double> hc((size_t)3 * n_cells);
+      CU(cudaMemcpy(hc.data(), d_centers.p, hc.size() * 8, cudaMemcpyDeviceToHost));
+      KdTreeHost tree;
+      build_kdtree(hc.data(), n_cells, tree);
+      if (d.n_internal > 0) {
+        // nodes with their children's splits alongside: {split, split(2i+1), split(2i+2), dimensions}
+        std::vector<double> fat((size_t)4 * d.n_internal, 0.0);
+        for (int i = 0; i < d.n_internal; ++i) {
+          unsigned long long dims = tree.sdim[i];
+          fat[4 * (size_t)i] = tree.split[i];
+          for (int c = 0; c < 2; ++c) {
+            const long long ch = 2LL * i + 1 + c;
+            if (ch < d.n_internal) { fat[4 * (size_t)i + 1 + c] = tree.split[ch]; dims |= (unsigned long long)tree.sdim[ch] << (2 + 2 * c); }
+          }
+          std::memcpy(&fat[4 * (size_t)i + 3], &dims, 8);
         }
-        std::memcpy(&fat[4 * (size_t)i + 3], &dims, 8);
+        CU(cudaMemcpy(d.fat, fat.data(), fat.size() * sizeof(double), cudaMemcpyHostToDevice));
       }
-      CU(cudaMalloc((void**)&d.fat, fat.size() * sizeof(double)));
-      CU(cudaMemcpy(d.fat, fat.data(), fat.size() * sizeof(double), cudaMemcpyHostToDevice));
+      if (!tree.box.empty()) CU(cudaMemcpy(d.box, tree.box.data(), tree.box.size() * sizeof(float), cudaMemcpyHostToDevice));
+      CU(cudaMemcpy(d.orig_of_dev, tree.orig_of_slot.data(), n_slots * 4, cudaMemcpyHostToDevice));
+    } else {
+      const int rc_tree = build_kdtree_device(d_centers.p, n_cells, d.fat, d.box, d.orig_of_dev, s);
+      if (rc_tree < 0) {
+        const cudaError_t ce = (cudaError_t)(-(rc_tree + 1000));
+        set_error(std::string("kd-tree build: ") + cudaGetErrorString(ce));
+        throw CudaFail{ce == cudaErrorMemoryAllocation ? IU_B200_ENOMEM : IU_B200_ECUDA};
+      }
+      g->n_launches += rc_tree;
     }
-    CU(cudaMalloc((void**)&d.box, std::max<size_t>(32, tree.box.size() * sizeof(float))));
-    if (!tree.box.empty()) CU(cudaMemcpy(d.box, tree.box.data(), tree.box.size() * sizeof(float), cudaMemcpyHostToDevice));
-    CU(cudaMemcpyAsync(d.orig_of_dev, tree.orig_of_slot.data(), n_slots * 4, cudaMemcpyHostToDevice, s));
+    g->tree_build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_tree).count();
     g->n_launches += launch_build_records(d, d_points.p, d_cells.p, d_neigh.p, d_centers.p, s);
     CU(cudaStreamSynchronize(s));
     d.points = d_points.take();
@@ -560,7 +577,7 @@ int create_from_arrays(int cell_type, int n_points, int n_cells, const double* p
       CU(cudaMalloc((void**)&d.icd, (size_t)n_cells * n_icd * 4));
       CU(cudaMemcpy(d.icd, icd, (size_t)n_cells * n_icd * 4, cudaMemcpyHostToDevice));
     }
-    g->mesh_bytes = (size_t)n_points * 24 + n_slots * (rec_stride(ppc) * 8 + 24 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + tree.box.size() * sizeof(float) +
+    g->mesh_bytes = (size_t)n_points * 24 + n_slots * (rec_stride(ppc) * 8 + 24 + 32 + 4) + ((size_t)n_cells + 1) * 4 + (size_t)d.n_internal * 32 + box_floats * sizeof(float) +
                     (size_t)n_points * d.pd_stride * 8 + (size_t)n_cells * (n_cd * 8 + n_icd * 4);
     init_pipeline(g);
     return IU_B200_OK;
@@ -1002,6 +1019,7 @@ int iu_b200_get_stats(iu_b200_grid* g, int64_t stats[IU_B200_N_STATS]) {
     stats[IU_B200_STAT_REPLICATE_US] = (int64_t)(g->replicate_ms * 1e3);
     stats[IU_B200_STAT_BOUNDS_ERRORS] = (int64_t)bounds_errors();
     stats[IU_B200_STAT_H2D_SKIPPED_BYTES] = (int64_t)g->h2d_skipped_bytes;
+    stats[IU_B200_STAT_TREE_BUILD_US] = (int64_t)(g->tree_build_ms * 1e3);
     // a multi-GPU handle reports the sums over its devices for the counters that add up
     for (iu_b200_grid* r : g->replicas) {
       int64_t rs[IU_B200_N_STATS];

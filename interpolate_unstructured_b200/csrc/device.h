@@ -157,6 +157,10 @@ int morton_end_bit(const DeviceGrid& g);
 // fills lists (n_vox x VOX_K) for the grid described by v; stats[0] = voxels flagged VOX_TREE, stats[1] = sum of list lengths
 int launch_build_voxels(const DeviceGrid& g, const VoxelGrid& v, int64_t n_vox, uint32_t* lists, unsigned long long* stats,
                         cudaStream_t s);
+// tree_build.cu: the nearest-centre kd-tree built on the device.  centers: device (3, n_cells); fat [4 (L-1)] doubles,
+// box [8 (2L-1)] floats and orig_of_dev [L LEAF] int32 are device arrays of the caller, L = ceil(n_cells / LEAF).
+// Returns the number of kernels launched, or -(cudaError_t) - 1000 on a CUDA error.  Synchronises s.
+int build_kdtree_device(const double* centers, int n_cells, double* fat, float* box, int32_t* orig_of_dev, cudaStream_t s);
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s);
 long long bounds_errors();   // builds with -DIU_CHECKED=1: index-range violations seen by the kernels so far; otherwise -1
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s);

@@ -415,3 +415,41 @@ def test_queries_on_vertices_edges_faces_and_centres(kind, n, jitter):
     got = g.iu_get_cell_through_neighbors(10 ** 6, r0, r1, ic0)
     for a, b in zip(got, want):
         assert np.array_equal(a, b, equal_nan=True)
+
+
+def test_device_built_kdtree_exact_search_all_sizes():
+    """tree_build.cu: the kd-tree is built on the device (level-synchronous: boxes, radix sort by (node, coordinate),
+    middle elements).  With the voxel table switched off every query runs the tree search, which must return the exact
+    nearest centre (ties -> lowest cell index) for leaf counts of every shape: 1 cell, fewer cells than a leaf, one
+    more than a leaf, non-powers of two, lattices full of ties, planar meshes; inside, outside and far-away queries."""
+    cases = [("quad", 1, 0.0), ("quad", 2, 0.0), ("quad", 3, 0.2), ("triangle", 2, 0.0), ("triangle", 3, 0.2), ("tetra", 1, 0.0),
+             ("tetra", 2, 0.1), ("tetra", 3, 0.0), ("tetra", 5, 0.1), ("quad", 37, 0.0), ("quad", 64, 0.2), ("triangle", 45, 0.2),
+             ("tetra", 11, 0.0), ("tetra", 13, 0.1)]
+    for kind, n, jitter in cases:
+        gen = {"tetra": meshgen.kuhn_tet_mesh, "quad": meshgen.quad_mesh, "triangle": meshgen.triangle_mesh}[kind]
+        pts, cells = gen(n, jitter=jitter, seed=7)
+        nb = api.build_cell_neighbors(cells, pts, kind)
+        pd = meshgen.smooth_fields(pts, 2)
+        g = api.Grid.from_arrays(kind, pts, cells, nb, pd)
+        o = OracleGrid.from_arrays(kind, pts, cells, nb, pd)
+        g.set_option(api.OPT_NN_VOXEL_DENSITY, 0)                      # kd-tree search only
+        assert g.stats()["nn_voxels"] == 0 and g.stats()["tree_build_us"] > 0
+        lo, hi = pts.min(0), pts.max(0)
+        ext = np.where(hi > lo, hi - lo, 0.0)
+        r = np.concatenate([meshgen.uniform_queries(20_000, lo - 0.3 * ext, hi + 0.3 * ext, seed=n),
+                            meshgen.uniform_queries(500, lo - 50 * ext - 1, hi + 50 * ext + 1, seed=n + 1),
+                            o.cell_centers, pts])
+        if kind != "tetra":
+            r[:20_500, 2] = 0.0
+        for sort in (0, 1):
+            g.set_option(api.OPT_SORT_QUERIES, sort)
+            idx = g.find_nearby_cell_kdtree(r)
+            oidx, best, second = o.nearest(r, "brute", nthreads=NT)
+            assert (idx == oidx).all(), (kind, n, jitter, sort, int((idx != oidx).sum()))
+        res, ic = g.iu_interpolate_at(r, [1, 2], var_at_r=np.full((len(r), 2), -1.0))
+        ores, oic = o.interpolate_at(r, [1, 2], var_at_r=np.full((len(r), 2), -1.0), nn="brute", nthreads=NT)
+        assert (ic == oic).all() and np.array_equal(res, ores), (kind, n, jitter)
+        # the voxel table built from this tree gives the same answers
+        g.set_option(api.OPT_NN_VOXEL_DENSITY, 400)
+        assert (g.find_nearby_cell_kdtree(r) == oidx).all(), (kind, n, jitter, "voxels")
+        g.close()
