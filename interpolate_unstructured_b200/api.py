@@ -290,8 +290,12 @@ class Grid:
             device = devices[0]
         ct = CELL_TYPES.get(cell_type, cell_type)
         points = _f64(points, (3,))
-        cells = np.ascontiguousarray(np.asarray(cells0, dtype=np.int64) + 1, dtype=np.int32)
-        neigh = np.ascontiguousarray(np.asarray(neighbors0, dtype=np.int64) + 1, dtype=np.int32)
+        def plus_one(a):          # 0-based -> 1-based in one pass (int32 input stays int32: index tables of 50M cells are 800 MB)
+            a = np.asarray(a)
+            if a.dtype == np.int32 and (a.size == 0 or a.max() < np.iinfo(np.int32).max):
+                return np.ascontiguousarray(np.add(a, 1, dtype=np.int32))
+            return np.ascontiguousarray(np.asarray(a, dtype=np.int64) + 1, dtype=np.int32)
+        cells, neigh = plus_one(cells0), plus_one(neighbors0)
         if cells.shape != neigh.shape or cells.ndim != 2:
             raise ValueError("cells and neighbors must both be (n_cells, points_per_cell)")
 

@@ -696,6 +696,7 @@ __global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, 
   __shared__ double s_c[8][3][VOX_GATHER];
   __shared__ int s_slot[8][VOX_GATHER];
   __shared__ int s_stack[8][72];
+  __shared__ double s_sd2[8][72];
   __shared__ unsigned char s_alive[8][VOX_GATHER];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const double inf = __longlong_as_double(0x7ff0000000000000LL);
@@ -716,18 +717,30 @@ __global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, 
     double D2 = inf;
     int count = 0, sp = 0;
     bool overflow = false;
-    s_stack[w][sp++] = 0;
-    __syncwarp();
-    while (sp > 0) {
-      const int node = s_stack[w][--sp];
-      __syncwarp();
-      const float* b = t.box + 8 * (size_t)node;
+    // A node is pushed together with the squared distance from the voxel box to the box of its centres, computed when
+    // its PARENT is expanded: the parent's fat node and both children's boxes (64 contiguous bytes) are fetched in one
+    // round trip instead of two dependent ones, and children beyond the current bound are never pushed.  D2 only
+    // shrinks, so the stored distance is re-checked against the bound of the moment when the node is popped.
+    auto box_d2 = [&](const float* b) {
+      float v[8];
+      asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                   : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(b));
       double d2 = 0;
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
-        const double g = fmax(fmax((double)__ldg(b + k) - bhi[k], blo[k] - (double)__ldg(b + 3 + k)), 0.0);
+        const double g = fmax(fmax((double)v[k] - bhi[k], blo[k] - (double)v[3 + k]), 0.0);
         d2 += g * g;
       }
+      return d2;
+    };
+    if (lane == 0) { s_stack[w][0] = 0; s_sd2[w][0] = 0.0; }
+    sp = 1;
+    __syncwarp();
+    while (sp > 0) {
+      --sp;
+      const int node = s_stack[w][sp];
+      const double d2 = s_sd2[w][sp];
+      __syncwarp();
       if (d2 > D2 * (1.0 + VOX_EPS)) continue;
       if (node >= t.n_internal) {
         const int base = (node - t.n_internal) * LEAF;
@@ -756,10 +769,14 @@ __global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, 
         if (count > VOX_GATHER) { overflow = true; count = VOX_GATHER; }
       } else {
         const D4 f = ld256(t.fat + 4 * (size_t)node);
+        const double dl = box_d2(t.box + 8 * (size_t)(2 * node + 1)), dr = box_d2(t.box + 8 * (size_t)(2 * node + 2));
         const int dim = __double2loint(f.w) & 3;
         const int near = (dim == 0 ? bc[0] : dim == 1 ? bc[1] : bc[2]) < f.x ? 0 : 1;
-        if (lane == 0) { s_stack[w][sp] = 2 * node + 2 - near; s_stack[w][sp + 1] = 2 * node + 1 + near; }
-        sp += 2;
+        const double bound = D2 * (1.0 + VOX_EPS);
+        const int c_far = 2 * node + 2 - near, c_near = 2 * node + 1 + near;
+        const double d_far = near ? dl : dr, d_near = near ? dr : dl;
+        if (!(d_far > bound)) { if (lane == 0) { s_stack[w][sp] = c_far; s_sd2[w][sp] = d_far; } ++sp; }
+        if (!(d_near > bound)) { if (lane == 0) { s_stack[w][sp] = c_near; s_sd2[w][sp] = d_near; } ++sp; }
         __syncwarp();
       }
     }
