@@ -682,7 +682,7 @@ __device__ __forceinline__ int nearest_center(const TreeView& t, float* s_lb,
 // keeps every centre that can be nearest OR tie for nearest in computed arithmetic.  Voxels with more than VOX_K
 // survivors (or more than VOX_GATHER gathered) are flagged VOX_TREE.
 // ------------------------------------------------------------------------------------------------
-constexpr int VOX_GATHER = 128;
+constexpr int VOX_GATHER = 160;
 constexpr double VOX_EPS = 1e-9, VOX_DELTA = 1e-3;
 
 __device__ __forceinline__ double warp_min(double v) {
@@ -691,6 +691,14 @@ __device__ __forceinline__ double warp_min(double v) {
   return v;
 }
 
+// One warp per BLOCK of 2 x 2 x 2 voxels.  The tree is traversed once for the union U of the block's (inflated) voxel
+// boxes - all 32 lanes of a warp evaluate the same box tests, so a traversal per voxel spent 41 % of the kernel's
+// instructions on redundant work (profiles/r02w_k_build_voxels_metrics.txt) - and the gathered centres are then filtered
+// for each voxel B of the block.  This is the same list a traversal for B alone produces: with
+// D2(B) = min_c maxdist^2(c, B) <= D2(U), every centre within (1 + eps) D2(B) of B is within (1 + eps) D2(U) of U
+// (mindist(c, U) <= mindist(c, B)), and so is the centre that attains D2(B); a gathered centre outside that set can never
+// remove one inside it (it would have to be closer than it for every point of B).  A block whose union gathers more than
+// VOX_GATHER centres falls back to one traversal per voxel.
 __global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, int64_t n_vox, uint32_t* __restrict__ lists,
                                                       unsigned long long* __restrict__ stats) {
   __shared__ double s_c[8][3][VOX_GATHER];
@@ -698,29 +706,28 @@ __global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, 
   __shared__ int s_stack[8][72];
   __shared__ double s_sd2[8][72];
   __shared__ unsigned char s_alive[8][VOX_GATHER];
+  __shared__ int s_out[8][VOX_K];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const double inf = __longlong_as_double(0x7ff0000000000000LL);
   unsigned long long n_flagged = 0, n_entries = 0;
-  for (int64_t vox = (int64_t)blockIdx.x * 8 + w; vox < n_vox; vox += (int64_t)gridDim.x * 8) {
-    int iv[3];
-    iv[0] = (int)(vox % vg.n[0]); iv[1] = (int)((vox / vg.n[0]) % vg.n[1]); iv[2] = (int)(vox / ((int64_t)vg.n[0] * vg.n[1]));
-    double blo[3], bhi[3], bc[3];
+  (void)n_vox;
+  int nb[3];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      if (vg.flat_mask >> k & 1) { blo[k] = bhi[k] = bc[k] = vg.flat_val[k]; }
-      else {
-        blo[k] = vg.lo[k] + ((double)iv[k] - VOX_DELTA) * vg.h[k];
-        bhi[k] = vg.lo[k] + ((double)iv[k] + 1.0 + VOX_DELTA) * vg.h[k];
-        bc[k] = 0.5 * (blo[k] + bhi[k]);
-      }
-    }
-    double D2 = inf;
-    int count = 0, sp = 0;
-    bool overflow = false;
-    // A node is pushed together with the squared distance from the voxel box to the box of its centres, computed when
-    // its PARENT is expanded: the parent's fat node and both children's boxes (64 contiguous bytes) are fetched in one
-    // round trip instead of two dependent ones, and children beyond the current bound are never pushed.  D2 only
-    // shrinks, so the stored distance is re-checked against the bound of the moment when the node is popped.
+  for (int k = 0; k < 3; ++k) nb[k] = (vg.n[k] + 1) / 2;
+  const int64_t n_blocks = (int64_t)nb[0] * nb[1] * nb[2];
+
+  double D2 = inf;
+  int count = 0;
+  bool overflow = false;
+
+  // gathers into s_c / s_slot every centre within (1 + eps) of the running D2 of the box [blo, bhi] (centre bc)
+  auto gather = [&](const double* blo, const double* bhi, const double* bc) {
+    D2 = inf; count = 0; overflow = false;
+    int sp = 0;
+    // A node is pushed together with the squared distance from the box to the box of its centres, computed when its
+    // PARENT is expanded: the parent's fat node and both children's boxes (64 contiguous bytes) are fetched in one round
+    // trip, and children beyond the current bound are never pushed.  D2 only shrinks, so the stored distance is
+    // re-checked against the bound of the moment when the node is popped.
     auto box_d2 = [&](const float* b) {
       float v[8];
       asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -781,14 +788,18 @@ __global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, 
       }
     }
     __syncwarp();
-    // survivors: within the final D2 and not dominated by any gathered centre
+  };
+
+  // the list of voxel `vox` = box [blo, bhi] from the gathered centres: within (1 + eps) D2v of the box and not beaten by
+  // another gathered centre over the whole box
+  auto emit = [&](int64_t vox, const double* blo, const double* bhi, double D2v, bool ovf) {
     int n_alive = 0;
-    if (!overflow) {
+    if (!ovf) {
       for (int i = lane; i < count; i += 32) {
         const double cx = s_c[w][0][i], cy = s_c[w][1][i], cz = s_c[w][2][i];
         const double gx = fmax(fmax(blo[0] - cx, cx - bhi[0]), 0.0), gy = fmax(fmax(blo[1] - cy, cy - bhi[1]), 0.0),
                      gz = fmax(fmax(blo[2] - cz, cz - bhi[2]), 0.0);
-        bool alive = (gx * gx + gy * gy) + gz * gz <= D2 * (1.0 + VOX_EPS);
+        bool alive = (gx * gx + gy * gy) + gz * gz <= D2v * (1.0 + VOX_EPS);
         const double ax = fmax(fabs(cx - blo[0]), fabs(cx - bhi[0])), ay = fmax(fabs(cy - blo[1]), fabs(cy - bhi[1])),
                      az = fmax(fabs(cz - blo[2]), fabs(cz - bhi[2]));
         const double margin = VOX_EPS * ((ax * ax + ay * ay) + az * az);
@@ -802,30 +813,73 @@ __global__ void __launch_bounds__(256) k_build_voxels(TreeView t, VoxelGrid vg, 
         s_alive[w][i] = alive ? 1 : 0;
       }
       __syncwarp();
-      // compact the survivors to the front (traversal order = nearest leaves first)
-      for (int i0 = 0; i0 < count; i0 += 32) {
+      for (int i0 = 0; i0 < count; i0 += 32) {   // survivors in traversal order (nearest leaves first)
         const int i = i0 + lane;
         const bool a = i < count && s_alive[w][i];
-        const int sl = i < count ? s_slot[w][i] : 0;
         const unsigned m = __ballot_sync(0xffffffffu, a);
         const int pos = n_alive + __popc(m & ((1u << lane) - 1u));
-        __syncwarp();
-        if (a && pos < VOX_K) s_slot[w][pos] = sl;   // pos <= i: only slots already read by this round are overwritten
+        if (a && pos < VOX_K) s_out[w][pos] = s_slot[w][i];
         n_alive += __popc(m);
-        __syncwarp();
       }
+      __syncwarp();
     }
-    const bool flagged = overflow || n_alive > VOX_K || n_alive == 0;
+    const bool flagged = ovf || n_alive > VOX_K || n_alive == 0;
     if (lane < VOX_K) {
       uint32_t e;
       if (flagged) e = lane == 0 ? VOX_TREE : VOX_END;
-      else if (lane < n_alive) e = (uint32_t)s_slot[w][lane];
-      else if (lane < ((n_alive + 3) & ~3)) e = (uint32_t)s_slot[w][n_alive - 1];   // pad the last group with a repeat
+      else if (lane < n_alive) e = (uint32_t)s_out[w][lane];
+      else if (lane < ((n_alive + 3) & ~3)) e = (uint32_t)s_out[w][n_alive - 1];   // pad the last group with a repeat
       else e = VOX_END;
       lists[(size_t)vox * VOX_K + lane] = e;
     }
     if (flagged) ++n_flagged; else n_entries += (unsigned long long)n_alive;
     __syncwarp();
+  };
+
+  // inflated box of the voxel range [i0, i1) per dimension (VOX_DELTA voxel sizes per side cover the rounding of the
+  // query's voxel index)
+  auto range_box = [&](const int* i0, const int* i1, double* blo, double* bhi, double* bc) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (vg.flat_mask >> k & 1) { blo[k] = bhi[k] = bc[k] = vg.flat_val[k]; }
+      else {
+        blo[k] = vg.lo[k] + ((double)i0[k] - VOX_DELTA) * vg.h[k];
+        bhi[k] = vg.lo[k] + ((double)i1[k] + VOX_DELTA) * vg.h[k];
+        bc[k] = 0.5 * (blo[k] + bhi[k]);
+      }
+    }
+  };
+
+  for (int64_t blk = (int64_t)blockIdx.x * 8 + w; blk < n_blocks; blk += (int64_t)gridDim.x * 8) {
+    int b0[3], b1[3];
+    b0[0] = 2 * (int)(blk % nb[0]); b0[1] = 2 * (int)((blk / nb[0]) % nb[1]); b0[2] = 2 * (int)(blk / ((int64_t)nb[0] * nb[1]));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) b1[k] = min(b0[k] + 2, vg.n[k]);
+    double ulo[3], uhi[3], uc[3];
+    range_box(b0, b1, ulo, uhi, uc);
+    gather(ulo, uhi, uc);
+    const bool block_overflow = overflow;
+    for (int vz = b0[2]; vz < b1[2]; ++vz)
+      for (int vy = b0[1]; vy < b1[1]; ++vy)
+        for (int vx = b0[0]; vx < b1[0]; ++vx) {
+          const int v0[3] = {vx, vy, vz}, v1[3] = {vx + 1, vy + 1, vz + 1};
+          double blo[3], bhi[3], bc[3];
+          range_box(v0, v1, blo, bhi, bc);
+          const int64_t vox = ((int64_t)vz * vg.n[1] + vy) * vg.n[0] + vx;
+          if (block_overflow) {          // too many centres around the block: one traversal for this voxel alone
+            gather(blo, bhi, bc);
+            emit(vox, blo, bhi, D2, overflow);
+            continue;
+          }
+          double m = inf;                // D2 of this voxel from the gathered centres (the centre that attains it is among them)
+          for (int i = lane; i < count; i += 32) {
+            const double cx = s_c[w][0][i], cy = s_c[w][1][i], cz = s_c[w][2][i];
+            const double ax = fmax(fabs(cx - blo[0]), fabs(cx - bhi[0])), ay = fmax(fabs(cy - blo[1]), fabs(cy - bhi[1])),
+                         az = fmax(fabs(cz - blo[2]), fabs(cz - bhi[2]));
+            m = fmin(m, (ax * ax + ay * ay) + az * az);
+          }
+          emit(vox, blo, bhi, warp_min(m), false);
+        }
   }
   if (lane == 0) {
     if (n_flagged) atomicAdd(stats, n_flagged);
@@ -1830,7 +1884,8 @@ int launch_build_voxels(const DeviceGrid& g, const VoxelGrid& v, int64_t n_vox, 
                         cudaStream_t s) {
   if (n_vox == 0) return 0;
   const TreeView t{g.fat, g.centers4, g.orig_of_dev, g.box, g.n_internal};
-  const int64_t need = (n_vox + 7) / 8;
+  const int64_t n_blocks = (int64_t)((v.n[0] + 1) / 2) * ((v.n[1] + 1) / 2) * ((v.n[2] + 1) / 2);   // 2 x 2 x 2 voxels per warp
+  const int64_t need = (n_blocks + 7) / 8;
   const int b = (int)std::min<int64_t>(need, (int64_t)sm_count() * 8);
   k_build_voxels<<<b, 256, 0, s>>>(t, v, n_vox, lists, stats);
   return 1;
