@@ -277,6 +277,18 @@ int iu_b200_interpolate_at_icell_batch_dev(iu_b200_grid* grid, int64_t n, const 
 int iu_b200_interpolate_and_cell_scalar_at_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int n_vars,
                                                      const int32_t* i_vars /* host */, int i_cell_var, double* var_at_r,
                                                      double* cell_res, int32_t* i_cell, void* stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  iu_b200_interpolate_at_batch_dev for
+ * n <= IU_B200_NOALLOC_MAX_QUERIES queries (same arguments, same results, queries processed in curve order through a
+ * permutation) that allocates NOTHING: its scratch - sort keys, permutation, radix-sort temporary storage, the ticket
+ * counter of the tile scheduler - lives in one static __device__ array of 24 MiB + 256 B inside the library, which every
+ * GPU that loads the library holds until exit.  Larger n is rejected with IU_B200_EINVAL.  Every call shares that array
+ * (whatever the grid): calls that overlap on the GPU - different streams, or two host threads with two grids - race on it;
+ * calls on one stream, or otherwise ordered on the device, are fine.  The per-kernel timing option is ignored. */
+#define IU_B200_NOALLOC_MAX_QUERIES 1048576
+int iu_b200_interpolate_at_batch_dev_noalloc(iu_b200_grid* grid, int64_t n, const double* r, int n_vars,
+                                             const int32_t* i_vars /* host */, double* var_at_r, int32_t* i_cell,
+                                             void* stream);
 int iu_b200_get_cell_scalar_at_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int i_var,
                                          int32_t* i_guess, double* res, void* stream);
 int iu_b200_get_icell_scalar_at_batch_dev(iu_b200_grid* grid, int64_t n, const double* r, int i_var,

@@ -102,6 +102,7 @@ _SIGNATURES = {
     "iu_b200_find_nearby_cell_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, c_vp, c_vp]),
     "iu_b200_get_cell_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, c_vp, c_vp]),
     "iu_b200_interpolate_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, c_vp, c_vp, c_vp]),
+    "iu_b200_interpolate_at_batch_dev_noalloc": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, c_vp, c_vp, c_vp]),
     "iu_b200_interpolate_at_icell_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, c_vp, c_vp, c_vp]),
     "iu_b200_interpolate_and_cell_scalar_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_ip, C.c_int, c_vp, c_vp, c_vp, c_vp]),
     "iu_b200_get_cell_scalar_at_batch_dev": (C.c_int, [c_vp, C.c_int64, c_vp, C.c_int, c_vp, c_vp, c_vp]),
@@ -631,6 +632,17 @@ class Grid:
         _check(lib().iu_b200_interpolate_at_batch_dev(self._h, n, _dev_ptr(r, "float64", 3 * n, "r"), len(iv), iv.ctypes.data_as(c_ip),
                                                       _dev_ptr(var_at_r, "float64", n * len(iv), "var_at_r"),
                                                       _dev_ptr(i_cell, "int32", n, "i_cell"), _cur_stream(self.device)))
+
+    NOALLOC_MAX_QUERIES = 1 << 20
+
+    def iu_interpolate_at_dev_noalloc(self, r, i_vars, var_at_r, i_cell):
+        """iu_interpolate_at_dev for at most NOALLOC_MAX_QUERIES queries with all scratch in a static device array of the
+        library: no cudaMalloc / cudaFree on the path (include/iu_b200.h)."""
+        n = i_cell.numel()
+        iv = np.ascontiguousarray(i_vars, dtype=np.int32).reshape(-1)
+        _check(lib().iu_b200_interpolate_at_batch_dev_noalloc(self._h, n, _dev_ptr(r, "float64", 3 * n, "r"), len(iv), iv.ctypes.data_as(c_ip),
+                                                              _dev_ptr(var_at_r, "float64", n * len(iv), "var_at_r"),
+                                                              _dev_ptr(i_cell, "int32", n, "i_cell"), _cur_stream(self.device)))
 
     def iu_interpolate_at_icell_dev(self, r, i_vars, var_at_r, i_cell):
         n = i_cell.numel()

@@ -1353,6 +1353,25 @@ int iu_b200_get_cell_through_neighbors_batch_dev(iu_b200_grid* g, int64_t n, int
   });
 }
 
+int iu_b200_interpolate_at_batch_dev_noalloc(iu_b200_grid* g, int64_t n, const double* r, int n_vars, const int32_t* i_vars,
+                                             double* var_at_r, int32_t* i_cell, void* stream) {
+  int rc = check_query_args(g, n, r, QM_INTERP, n_vars, i_vars, 0);
+  if (rc != IU_B200_OK || n == 0) return rc;
+  if (!var_at_r || !i_cell) { set_error("null output array"); return IU_B200_EINVAL; }
+  if (n > NOALLOC_MAX_QUERIES) {
+    set_error("iu_b200_interpolate_at_batch_dev_noalloc: n exceeds IU_B200_NOALLOC_MAX_QUERIES (1048576); split the batch or use "
+              "iu_b200_interpolate_at_batch_dev");
+    return IU_B200_EINVAL;
+  }
+  std::lock_guard<std::mutex> lock(g->mu);
+  DeviceGuard guard(g->device);
+  const int launches = launch_query_noalloc(g->dg, make_args(g, QM_INTERP, n, r, n_vars, i_vars, 0, i_cell, var_at_r, nullptr), (cudaStream_t)stream);
+  if (launches < 0) return IU_B200_ECUDA;
+  g->n_launches += launches;
+  g->n_queries += n;
+  return IU_B200_OK;
+}
+
 int iu_b200_check_dev(iu_b200_grid* g, void* stream) {
   if (!g) { set_error("null grid"); return IU_B200_EINVAL; }
   std::lock_guard<std::mutex> lock(g->mu);

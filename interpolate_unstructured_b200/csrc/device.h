@@ -99,6 +99,7 @@ struct QueryArgs {
   int max_steps = 1 << 20;
   int dynamic = 0;                  // 1: draw tiles of consecutive queries from a ticket counter (sorted batches only)
   int tiles_per_warp = 0;           // dynamic = 1: warps retire after this many tiles (0 = persistent CTAs)
+  unsigned long long* ticket = nullptr;   // dynamic = 1: the ticket counter to use; null = the grid's own (every existing caller)
 };
 
 struct WalkArgs {
@@ -164,6 +165,12 @@ int build_kdtree_device(const double* centers, int n_cells, double* fat, float* 
 int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s);
 long long bounds_errors();   // builds with -DIU_CHECKED=1: index-range violations seen by the kernels so far; otherwise -1
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s);
+// The sorted, ticket-scheduled query pass with ALL of its scratch (sort keys, permutation, radix-sort temporary storage,
+// ticket counter) in a file-scope static __device__ array of kernels.cu: no cudaMalloc / cudaFree anywhere on the path.
+// a.n <= NOALLOC_MAX_QUERIES.  The device of the grid must be current.  Returns the number of kernels launched, or a
+// negative value with set_error() called.
+constexpr int64_t NOALLOC_MAX_QUERIES = 1 << 20;
+int launch_query_noalloc(const DeviceGrid& g, QueryArgs a, cudaStream_t s);
 int launch_ray_length_sample(int64_t n, int n_samples, const double* r0, const double* r1, double* sum, cudaStream_t s);
 int launch_trace_seeds(int64_t n, int ndim, int nt, int max_steps, const double* y, double* r, cudaStream_t s);
 int launch_trace(const DeviceGrid& g, const TraceArgs& a, cudaStream_t s);

@@ -20,6 +20,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include <cstdlib>
+#include <string>
 
 #include "device.h"
 
@@ -1935,7 +1936,7 @@ int launch_query(const DeviceGrid& g, const QueryArgs& a, cudaStream_t s) {
         if (a.ivars[v] % 4 != 0 || a.ivars[v + 2] != a.ivars[v] + 2) P.pairs = 1;
     }
   }
-  P.ticket = a.dynamic ? g.counters + CNT_TICKET : nullptr;
+  P.ticket = a.dynamic ? (a.ticket ? a.ticket : g.counters + CNT_TICKET) : nullptr;
   P.sched = a.dynamic;
   P.tiles_per_warp = a.tiles_per_warp;
   if (g.cell_type == IU_TRIANGLE_CT) launch_query_ct<IU_TRIANGLE_CT>(a.mode, P, g.depth, s);
@@ -1982,6 +1983,61 @@ int launch_ray_length_sample(int64_t n, int n_samples, const double* r0, const d
   cudaMemsetAsync(sum, 0, sizeof(double), s);
   k_ray_length_sample<<<(n_samples + 255) / 256, 256, 0, s>>>(n, n_samples, r0, r1, sum);
   return 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// The allocation-free query pass (iu_b200_interpolate_at_batch_dev_noalloc; no counterpart in the reference, added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).
+// Scratch layout inside g_noalloc_scratch, all offsets multiples of 256 bytes:
+//   [0, 256)            ticket counter of the tile scheduler (cleared by every call)
+//   4 x 4 MiB           curve keys, sorted keys, query indices, permutation for up to NOALLOC_MAX_QUERIES queries
+//   rest (8 MiB)        temporary storage of cub::DeviceRadixSort::SortPairs
+// Every GPU that loads the library holds the 24 MiB + 256 B until exit.  Every call shares the array: calls that overlap
+// on the GPU (different streams, different grids) race on it.
+// ------------------------------------------------------------------------------------------------
+constexpr size_t NOALLOC_ARR = (size_t)NOALLOC_MAX_QUERIES * 4;
+constexpr size_t NOALLOC_TEMP = (size_t)8 << 20;
+constexpr size_t NOALLOC_BYTES = 256 + 4 * NOALLOC_ARR + NOALLOC_TEMP;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+// In host code g_noalloc_scratch is only a stand-in for the symbol: its device address is looked up once per device,
+// with that device current.
+static unsigned char* noalloc_scratch_ptr() {
+  static unsigned char* ptr[64] = {nullptr};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("noalloc: cannot identify the current device"); return nullptr; }
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) { set_error(std::string("noalloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e)); return nullptr; }
+    ptr[dev] = (unsigned char*)p;
+  }
+  return ptr[dev];
+}
+
+int launch_query_noalloc(const DeviceGrid& g, QueryArgs a, cudaStream_t s) {
+  if (a.n == 0) return 0;
+  if (a.n < 0 || a.n > NOALLOC_MAX_QUERIES) { set_error("noalloc: more than 1048576 queries in one call"); return -1; }
+  unsigned char* base = noalloc_scratch_ptr();
+  if (!base) return -1;
+  unsigned long long* ticket = reinterpret_cast<unsigned long long*>(base);
+  uint32_t* keys = reinterpret_cast<uint32_t*>(base + 256);
+  uint32_t* keys_alt = reinterpret_cast<uint32_t*>(base + 256 + NOALLOC_ARR);
+  uint32_t* idx = reinterpret_cast<uint32_t*>(base + 256 + 2 * NOALLOC_ARR);
+  uint32_t* perm = reinterpret_cast<uint32_t*>(base + 256 + 3 * NOALLOC_ARR);
+  void* temp = base + 256 + 4 * NOALLOC_ARR;
+  const size_t need = sort_temp_bytes(a.n, morton_end_bit(g));   // a size query: allocates nothing
+  if (need > NOALLOC_TEMP) { set_error("noalloc: the radix sort wants more temporary storage than the static scratch reserves"); return -1; }
+  int launches = launch_morton_sort(g, a.n, a.r, a.mode == QM_NEAREST ? nullptr : a.i_cell, keys, keys_alt, idx, perm, temp, NOALLOC_TEMP,
+                                    nullptr, s);
+  a.perm = perm;
+  a.dynamic = 1;
+  a.tiles_per_warp = 0;
+  a.ticket = ticket;       // launch_query_static clears it (cudaMemsetAsync on the stream) before the kernel starts
+  launches += launch_query(g, a, s);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error(std::string("noalloc: ") + cudaGetErrorString(e)); return -1; }
+  return launches;
 }
 
 int launch_walk(const DeviceGrid& g, const WalkArgs& a, cudaStream_t s) {
