@@ -49,7 +49,9 @@ __device__ long long g_lim[4] = {0, 0, 0, 0};   // device slots, points, voxels,
 #endif
 constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #ifndef IU_QUERY_MIN_BLOCKS
-#define IU_QUERY_MIN_BLOCKS 4   // resident CTAs per SM the hot kernel is compiled for (64 registers per thread)
+#define IU_QUERY_MIN_BLOCKS 3   // resident CTAs per SM the hot kernel is compiled for: 3 = 80 registers, no spills.  With the
+                                // round-1 tree search 4 CTAs at 64 registers (64 B of spills) were faster; with the voxel-table
+                                // search 3 are: C3 +1.9 %, C5 +6 %, C4 +3 %, C2 +2 % (profiles/experiments/r03b_*)
 #endif
 #ifndef IU_SELP
 #define IU_SELP 1          // 1: branch-free selection of the query coordinate of a node's split dimension
@@ -1273,7 +1275,7 @@ __global__ void __launch_bounds__(QUERY_THREADS, IU_QUERY_MIN_BLOCKS) k_query(co
   extern __shared__ float s_lb[];   // [tree depth][QUERY_THREADS] plane-distance lower bounds (nearest_center)
   // SCHED = 1: warps draw STILE consecutive (sorted) queries at a time from the ticket counter
 #ifndef IU_STILE
-#define IU_STILE 128
+#define IU_STILE 64    // queries per ticket tile (with 3 CTAs per SM 64 beats 128: C5 +3 %, the others equal)
 #endif
   constexpr int STILE = IU_STILE;
   const int lane = threadIdx.x & 31;
