@@ -58,7 +58,7 @@ constexpr int QUERY_THREADS = IU_QUERY_THREADS;
 #endif
 
 #ifndef IU_WALK_256
-#define IU_WALK_256 0   // 1: 32-byte loads in the walk too (6 instead of 12 per cell, but spills at 64 registers: slower)
+#define IU_WALK_256 0   // 1: 32-byte loads in the walk too (6 instead of 12 per cell; spills at 64 and at 80 registers: slower both times, profiles/experiments/r03d_*)
 #endif
 #ifndef IU_HILBERT
 #define IU_HILBERT 1    // 1: queries of 3-D meshes are ordered along a Hilbert curve, 0: Morton order
@@ -1256,7 +1256,7 @@ __device__ __forceinline__ void emit_result(const QueryKernelParams& P, int64_t 
 // `perm`; the dynamic shared memory holds the per-thread plane bounds of the kd-tree search (nearest_center), which only
 // the queries without a voxel list run.
 // SCHED = 0: static grid-stride assignment (unsorted batches).  SCHED = 1 (sorted batches): every
-// warp draws tiles of 128 consecutive sorted queries from a global ticket counter, so that all
+// warp draws tiles of IU_STILE (64) consecutive sorted queries from a global ticket counter, so that all
 // queries in flight on the GPU stay within one narrow window of the Morton order whatever the
 // speed differences between warps and SMs.
 // A walk whose FIRST iteration reads precomputed numerators (p_k - centre) . n_k instead of the start cell's vertices
